@@ -1,0 +1,226 @@
+"""CPU oracle for the ColXLIP MaxSim-loss hot path.  TEST INFRASTRUCTURE ONLY.
+
+This module is a plain-PyTorch fp32 restatement of the reference algorithm.  It is
+the *checker* the CUDA path is compared against; it is never the thing shipped or
+measured.  Only ``tests/``, ``__graft_entry__.smoke()`` and ``bench.py``'s
+``cpu_baseline`` / ``--impl reference`` legs may import it.  The product package
+``colxlip_b200`` must never import anything from ``oracle/``.
+
+Parity status: **pinned by execution of the reference itself** (the reference
+ships no tests, golden vectors or fixtures -- SURVEY.md section 4).  The script
+``tests/golden/make_golden.py`` imports ``/root/reference/src/colxlip/loss.py`` by
+path in the build container, runs it on seeded inputs and commits the resulting
+vectors under ``tests/golden/``; ``tests/test_oracle_golden.py`` checks every
+function below against those vectors.
+
+Reference lines followed (all relative to /root/reference/src/colxlip/):
+  maxsim_rowmax / maxsim_scores(masked)  loss.py:34-44   (einsum, max, !=0 mask, +1e-8)
+  maxsim_scores(mean)                    model.py:626-628 (einsum, max, plain mean)
+  gather_scaling                         loss.py:48-92    (semantics probed)
+  ColClipLossOracle.get_logits           loss.py:223-269
+  ColClipLossOracle.forward              loss.py:271-296
+  compute_retrieval                      train.py:457-508
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, Optional, Sequence, Tuple
+
+import numpy as np
+import torch
+import torch.nn.functional as F
+
+MASKED = 0  # loss.py:38-44  (count of non-zero maxima + 1e-8)
+MEAN = 1    # model.py:628   (plain mean over all T tokens)
+
+
+def maxsim_rowmax(img_tok: torch.Tensor, txt_tok: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Per text token: best patch similarity and its (first) index.
+
+    img_tok [Bi,P,D], txt_tok [Bt,T,D] -> (mx [Bt,Bi,T], arg [Bt,Bi,T] int64).
+    Follows loss.py:34-35: the contraction is 'mnd,kqd->mknq' and the max runs over
+    the patch axis q; ``torch.max`` returns the first maximal index on ties.
+    Done one text at a time so the [Bt,Bi,T,P] tensor is never materialised.
+    """
+    Bi, P, D = img_tok.shape
+    Bt, T, _ = txt_tok.shape
+    flat_img = img_tok.reshape(Bi * P, D)
+    mx = torch.empty(Bt, Bi, T, dtype=img_tok.dtype)
+    arg = torch.empty(Bt, Bi, T, dtype=torch.int64)
+    for m in range(Bt):
+        sim = (txt_tok[m] @ flat_img.T).view(T, Bi, P)           # [T,Bi,P]
+        v, i = torch.max(sim, dim=2)                              # [T,Bi]
+        mx[m] = v.T
+        arg[m] = i.T
+    return mx, arg
+
+
+def maxsim_scores(img_tok: torch.Tensor, txt_tok: torch.Tensor, mode: int = MASKED) -> torch.Tensor:
+    """S[Bt,Bi].  mode=MASKED follows loss.py:38-44, mode=MEAN follows model.py:628.
+
+    Differentiable (autograd flows through the selected maxima exactly as it does
+    through ``torch.max`` in the reference).
+    """
+    sim = torch.einsum("mnd,kqd->mknq", txt_tok, img_tok)
+    mx = sim.max(dim=3).values
+    if mode == MEAN:
+        return mx.mean(dim=-1)
+    nz = (mx != 0).to(torch.float32)
+    return mx.sum(dim=2) / (nz.sum(dim=2) + 1e-8)
+
+
+def maxsim_scores_blockwise(img_tok, txt_tok, mode: int = MASKED, block: int = 64) -> torch.Tensor:
+    """Same values as :func:`maxsim_scores` without the [Bt,Bi,T,P] tensor."""
+    Bt, Bi = txt_tok.shape[0], img_tok.shape[0]
+    out = torch.empty(Bt, Bi, dtype=torch.float32)
+    for m0 in range(0, Bt, block):
+        for k0 in range(0, Bi, block):
+            out[m0:m0 + block, k0:k0 + block] = maxsim_scores(
+                img_tok[k0:k0 + block].float(), txt_tok[m0:m0 + block].float(), mode)
+    return out
+
+
+def top2_gap(img_tok: torch.Tensor, txt_tok: torch.Tensor) -> torch.Tensor:
+    """Gap between best and second-best patch similarity, [Bt,Bi,T].
+
+    Used by the tests to classify argmax mismatches: a mismatch is only tolerated
+    where the oracle's own top-2 scores tie within tolerance (north_star).
+    """
+    Bi, P, D = img_tok.shape
+    Bt, T, _ = txt_tok.shape
+    gap = torch.empty(Bt, Bi, T)
+    flat_img = img_tok.reshape(Bi * P, D)
+    for m in range(Bt):
+        sim = (txt_tok[m] @ flat_img.T).view(T, Bi, P)
+        if P == 1:
+            gap[m] = float("inf")
+            continue
+        top = sim.topk(2, dim=2).values
+        gap[m] = (top[..., 0] - top[..., 1]).T
+    return gap
+
+
+def infonce_pair(logits: torch.Tensor) -> torch.Tensor:
+    """(CE(rows) + CE(cols)) / 2 against the diagonal -- loss.py:285-293."""
+    labels = torch.arange(logits.shape[0])
+    return (F.cross_entropy(logits, labels) + F.cross_entropy(logits.T, labels)) / 2
+
+
+class ColClipLossOracle:
+    """Single-process restatement of ColClipLoss (loss.py:184-296), world_size == 1."""
+
+    def __init__(self, alpha: float = 0.5):
+        self.alpha = alpha
+
+    def get_logits(self, image_features, text_features, token_image_features,
+                   token_text_features, logit_scale, logit_bias=None) -> Dict[str, torch.Tensor]:
+        logits_per_image = logit_scale * image_features @ text_features.T            # loss.py:259
+        logits_per_text = logits_per_image.T
+        logits_per_text_token = logit_scale * maxsim_scores(token_image_features,    # loss.py:262
+                                                            token_text_features, MASKED)
+        logits_per_image_token = logits_per_text_token.T
+        if logit_bias is not None:
+            # loss.py:265-267 adds the bias in place to logits_per_image AND to
+            # logits_per_text, which is a transposed *view* of the same storage, so the
+            # reference's global logits end up with 2x the bias (pinned by golden vector).
+            logits_per_image = logits_per_image + 2 * logit_bias
+            logits_per_text = logits_per_image.T
+        return {"logits_per_image": logits_per_image, "logits_per_text": logits_per_text,
+                "logits_per_image_token": logits_per_image_token,
+                "logits_per_text_token": logits_per_text_token}
+
+    def __call__(self, image_features, text_features, token_image_features,
+                 token_text_features, logit_scale, output_dict: bool = False):
+        out = self.get_logits(image_features, text_features, token_image_features,
+                              token_text_features, logit_scale)
+        g = infonce_pair(out["logits_per_image"])
+        t = infonce_pair(out["logits_per_text_token"])
+        total = self.alpha * g + (1 - self.alpha) * t
+        if output_dict:
+            return {"global_contrastive_loss": g, "token_contrastive_loss": t, "total_loss": total}
+        return total
+
+
+def loss_and_grads(image_features, text_features, token_image_features, token_text_features,
+                   logit_scale: float, alpha: float = 0.5):
+    """fp32 loss values and gradients w.r.t. the five inputs (autograd of the restatement)."""
+    xs = [t.detach().clone().float().requires_grad_() for t in
+          (image_features, text_features, token_image_features, token_text_features)]
+    ls = torch.tensor(float(logit_scale), requires_grad=True)
+    out = ColClipLossOracle(alpha)(*xs, ls, output_dict=True)
+    out["total_loss"].backward()
+    return ({k: v.detach() for k, v in out.items()},
+            {"image_features": xs[0].grad, "text_features": xs[1].grad,
+             "token_image_features": xs[2].grad, "token_text_features": xs[3].grad,
+             "logit_scale": ls.grad})
+
+
+def maxsim_closed_form_grads(img_tok, txt_tok, dS, mode: int = MASKED):
+    """Closed-form backward of maxsim_scores: no autograd, numpy-style loops.
+
+    cnt = nnz + 1e-8 (or T), w = dS / cnt,
+    dTxt[m,n] = sum_k w[m,k] img[k,q*],  dImg[k,q] = sum_{m,n:q*=q} w[m,k] txt[m,n].
+    """
+    mx, arg = maxsim_rowmax(img_tok.float(), txt_tok.float())
+    Bt, Bi, T = mx.shape
+    if mode == MEAN:
+        cnt = torch.full((Bt, Bi), float(T))
+    else:
+        cnt = (mx != 0).float().sum(dim=2) + 1e-8
+    w = dS / cnt
+    dtxt = torch.zeros_like(txt_tok, dtype=torch.float32)
+    dimg = torch.zeros_like(img_tok, dtype=torch.float32)
+    for m in range(Bt):
+        for k in range(Bi):
+            q = arg[m, k]                                    # [T]
+            dtxt[m] += w[m, k] * img_tok[k, q].float()
+            dimg[k].index_add_(0, q, w[m, k] * txt_tok[m].float())
+    return dtxt, dimg
+
+
+def gather_scaling(gather_with_grad: bool, world_size: int) -> float:
+    """Local-feature gradient = this factor x the single-process slice."""
+    return float(world_size) if gather_with_grad else 1.0
+
+
+def compute_retrieval(similarity_scores: torch.Tensor, txt2img: Sequence[int],
+                      img2txt: Sequence[Sequence[int]]) -> Dict[str, float]:
+    """Recall@k / rank statistics; restates train.py:457-508 with vectorised rank search.
+
+    similarity_scores is [N_img, N_txt] (i2t); its transpose is used for t2i.
+    """
+    i2t = similarity_scores.float()
+    t2i = i2t.T
+    t2i_ranks = np.zeros(t2i.shape[0])
+    for t, row in enumerate(t2i):
+        order = torch.argsort(row, descending=True)
+        t2i_ranks[t] = int((order == txt2img[t]).nonzero()[0, 0])
+    i2t_ranks = np.zeros(i2t.shape[0])
+    for i, row in enumerate(i2t):
+        order = torch.argsort(row, descending=True)
+        pos = torch.empty_like(order)
+        pos[order] = torch.arange(order.numel())
+        i2t_ranks[i] = min(int(pos[j]) for j in img2txt[i])
+
+    def rep(r, name):
+        return {f"{name}_R@1": float((r < 1).mean()), f"{name}_R@5": float((r < 5).mean()),
+                f"{name}_R@10": float((r < 10).mean()), f"{name}_mean_rank": float(r.mean() + 1),
+                f"{name}_median_rank": float(math.floor(np.median(r)) + 1)}
+
+    return {**rep(t2i_ranks, "text_to_image"), **rep(i2t_ranks, "image_to_text")}
+
+
+def synth_inputs(B: int, P: int, T: int, D: int, seed: int = 1234, pad_text: bool = False,
+                 Bt: Optional[int] = None):
+    """SURVEY 8(d) synthetic inputs: L2-normalised Gaussian rows, optional zero-padded tails."""
+    g = torch.Generator().manual_seed(seed)
+    Bt = B if Bt is None else Bt
+    tok_img = F.normalize(torch.randn(B, P, D, generator=g), dim=-1)
+    tok_txt = F.normalize(torch.randn(Bt, T, D, generator=g), dim=-1)
+    img = F.normalize(torch.randn(B, D, generator=g), dim=-1)
+    txt = F.normalize(torch.randn(Bt, D, generator=g), dim=-1)
+    if pad_text:
+        lens = torch.randint(min(4, T), T + 1, (Bt,), generator=g)
+        mask = torch.arange(T)[None, :] < lens[:, None]
+        tok_txt = tok_txt * mask[..., None]
+    return img, txt, tok_img, tok_txt
