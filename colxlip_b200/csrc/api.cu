@@ -1,0 +1,177 @@
+// extern "C" boundary of libcolxlip_b200.so (see include/colxlip_b200.h).
+#include <stdio.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace cxl {
+
+static thread_local char g_cuda_err[512] = "";
+
+void set_cuda_error(cudaError_t e, const char* where) {
+  snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
+}
+
+int num_sms() {
+  static int cached[64] = {0};
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return 148;
+  if (cached[dev] == 0) {
+    int n = 0;
+    if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = 148;
+    cached[dev] = n;
+  }
+  return cached[dev];
+}
+
+int img_row_stride(int P);
+int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
+                  float* cnt, void* argmax, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream);
+int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
+                   float* cnt, void* argmax, cudaStream_t stream);
+int maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
+               const float* gscale, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode, int p_stride,
+               int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img, cudaStream_t stream);
+size_t infonce_workspace_bytes(int B_loc, int B);
+int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse, float* col_max,
+                  float* col_sum, float* diag, void* ws, size_t ws_bytes, cudaStream_t stream);
+int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                 const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, cudaStream_t stream);
+int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
+              int D, void* dst, cudaStream_t stream);
+int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
+                   const int* target, int* rank_out, cudaStream_t stream);
+
+static int device_ok() {
+  int dev = 0, major = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return CXL_ERR_NO_DEVICE;
+  if (cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, dev) != cudaSuccess) return CXL_ERR_NO_DEVICE;
+  return major == 10 ? CXL_OK : CXL_ERR_NO_DEVICE;
+}
+
+}  // namespace cxl
+
+using namespace cxl;
+
+extern "C" {
+
+const char* cxl_strerror(int code) {
+  switch (code) {
+    case CXL_OK: return "ok";
+    case CXL_ERR_INVALID_ARG: return "invalid argument";
+    case CXL_ERR_UNSUPPORTED: return "unsupported shape or dtype for this build";
+    case CXL_ERR_CUDA: return "CUDA call failed (see cxl_last_cuda_error)";
+    case CXL_ERR_NO_DEVICE: return "no sm_100 (Blackwell B200) device; there is no CPU fallback";
+    case CXL_ERR_WORKSPACE: return "workspace too small";
+    default: return "unknown error";
+  }
+}
+
+const char* cxl_last_cuda_error(void) { return g_cuda_err; }
+
+int cxl_version(void) { return 100; }
+
+int cxl_device_check(void) { return device_ok(); }
+
+int cxl_argmax_elem_bytes(int P) { return P > 256 ? 2 : 1; }
+
+int cxl_img_row_stride(int P) { return img_row_stride(P); }
+
+int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride, int items,
+                  int n, int n_pad, int D, void* dst, void* stream) {
+  if (src == nullptr || dst == nullptr) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return pack_bf16(src, src_dtype, src_item_stride, src_row_stride, items, n, n_pad, D, dst,
+                   static_cast<cudaStream_t>(stream));
+}
+
+int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
+                   float* S, float* cnt, void* argmax, void* stream) {
+  if (txt == nullptr || img == nullptr || S == nullptr) return CXL_ERR_INVALID_ARG;
+  if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
+  if (static_cast<long long>(Bt) * T >= (1LL << 31) || static_cast<long long>(Bi) * P >= (1LL << 31))
+    return CXL_ERR_UNSUPPORTED;
+  if (mean_mode != CXL_MEAN_MASKED && mean_mode != CXL_MEAN_PLAIN) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  if (dtype == CXL_DTYPE_BF16) return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, nullptr, 0, 0, st);
+  if (dtype == CXL_DTYPE_F32)
+    return maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
+                          cnt, argmax, st);
+  return CXL_ERR_INVALID_ARG;
+}
+
+int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
+                   const float* gscale_dev, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode, int ld_pairs,
+                   int k_off, float* dtxt, float* dimg, int accumulate_img, void* stream) {
+  if (txt == nullptr || img == nullptr || argmax == nullptr || dS == nullptr) return CXL_ERR_INVALID_ARG;
+  if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  return maxsim_bwd(txt, img, argmax, dS, cnt, gscale_dev, Bt, Bi, T, P, D, dtype, mean_mode, p_stride, ld_pairs, k_off,
+                    dtxt, dimg, accumulate_img, static_cast<cudaStream_t>(stream));
+}
+
+size_t cxl_infonce_workspace_bytes(int B_loc, int B) { return infonce_workspace_bytes(B_loc, B); }
+
+int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse,
+                      float* col_max, float* col_sum, float* diag, void* ws, size_t ws_bytes, void* stream) {
+  if (!X || !scale_dev || !row_lse || !col_max || !col_sum || !diag || !ws) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return infonce_stats(X, scale_dev, B_loc, B, row0, row_lse, col_max, col_sum, diag, ws, ws_bytes,
+                       static_cast<cudaStream_t>(stream));
+}
+
+int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                     const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, void* stream) {
+  if (!X || !scale_dev || !coef_dev || !row_lse || !col_lse || !dX || !dscale_accum) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, dX, dscale_accum,
+                      static_cast<cudaStream_t>(stream));
+}
+
+int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
+                       const int* target, int* rank_out, void* stream) {
+  if (!scores || !target || !rank_out) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return rank_of_target(scores, row_stride, col_stride, rows, cols, target, rank_out, static_cast<cudaStream_t>(stream));
+}
+
+// Debug aid: run the tensor-core kernel on ONE text tile x ONE image tile (P = n_tile columns,
+// T = 128 rows) and dump the raw fp32 accumulators.  S/cnt scratch are allocated by the caller
+// through `out` being followed by nothing: we use stream-ordered temporaries here instead.
+int cxl_debug_tile(const void* txt_bf16, const void* img_bf16, int rowsA, int rowsB, int D, int n_tile, float* out,
+                   void* stream) {
+  if (!txt_bf16 || !img_bf16 || !out) return CXL_ERR_INVALID_ARG;
+  if (rowsA < 1 || rowsA > 128 || rowsB < 129 || rowsB > 256) return CXL_ERR_INVALID_ARG;  // single-image tile path
+  (void)n_tile;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  cudaStream_t st = static_cast<cudaStream_t>(stream);
+  float* scratch = nullptr;
+  CXL_CUDA_CHECK(cudaMallocAsync(&scratch, 2 * sizeof(float), st));
+  // one "text" of rowsA tokens against one "image" of rowsB patches
+  rc = maxsim_fwd_tc(txt_bf16, img_bf16, 1, 1, rowsA, rowsB, D, CXL_MEAN_PLAIN, scratch, scratch + 1, nullptr, out, 0, 0,
+                     st);
+  cudaFreeAsync(scratch, st);
+  return rc;
+}
+
+// Test hook: tensor-core forward with explicit scheduling overrides (stream-A mode, grid size).
+int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
+                         float* cnt, void* argmax, int force_stream_a, int force_grid, void* stream) {
+  if (txt == nullptr || img == nullptr || S == nullptr) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, nullptr, force_stream_a, force_grid,
+                       static_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,180 @@
+// K3: logit scale + symmetric InfoNCE (row- and column-softmax cross-entropy against the
+// diagonal) over a [B_loc, B] block of unscaled logits, plus its gradient.  HBM-bound.
+//
+// Replaces `logit_scale * S`, `.T` and the four F.cross_entropy calls of the reference
+// (loss.py:252-263, 285-293) and their autograd (log_softmax / nll_loss backward).
+// Rows are this rank's texts (global row index row0 + m), columns are all B images.
+#include "common.cuh"
+
+namespace cxl {
+
+// online (max, sum exp) pair
+struct MS {
+  float m, s;
+};
+__device__ __forceinline__ MS ms_combine(MS a, MS b) {
+  const float mx = fmaxf(a.m, b.m);
+  if (mx == -INFINITY) return MS{-INFINITY, 0.f};
+  return MS{mx, a.s * expf(a.m - mx) + b.s * expf(b.m - mx)};
+}
+__device__ __forceinline__ void ms_push(MS& a, float v) {
+  if (v > a.m) {
+    a.s = a.s * expf(a.m - v) + 1.f;
+    a.m = v;
+  } else {
+    a.s += expf(v - a.m);
+  }
+}
+
+// ---- row log-sum-exp: one CTA per row ----
+__global__ void __launch_bounds__(256) infonce_row_kernel(const float* __restrict__ X, const float* __restrict__ scale_p,
+                                                          int B, int row0, float* __restrict__ row_lse,
+                                                          float* __restrict__ diag) {
+  const int m = blockIdx.x;
+  const float scale = *scale_p;
+  const float* x = X + static_cast<size_t>(m) * B;
+  MS acc{-INFINITY, 0.f};
+  const int nvec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) ? (B >> 2) : 0;
+  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    ms_push(acc, scale * v.x); ms_push(acc, scale * v.y); ms_push(acc, scale * v.z); ms_push(acc, scale * v.w);
+  }
+  for (int i = nvec * 4 + threadIdx.x; i < B; i += blockDim.x) ms_push(acc, scale * x[i]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    MS other{__shfl_xor_sync(0xffffffffu, acc.m, o), __shfl_xor_sync(0xffffffffu, acc.s, o)};
+    acc = ms_combine(acc, other);
+  }
+  __shared__ MS part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = acc;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    MS t = part[0];
+    for (int w = 1; w < (blockDim.x >> 5); ++w) t = ms_combine(t, part[w]);
+    row_lse[m] = t.m + logf(t.s);
+    diag[m] = scale * x[row0 + m];
+  }
+}
+
+// ---- column (max, sumexp) partials over a block of rows: thread owns 4 adjacent columns ----
+static constexpr int kColRowsPerBlock = 128;
+__global__ void __launch_bounds__(128) infonce_col_partial_kernel(const float* __restrict__ X,
+                                                                  const float* __restrict__ scale_p, int B_loc, int B,
+                                                                  float* __restrict__ pmax, float* __restrict__ psum) {
+  const int c0 = (blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (c0 >= B) return;
+  const float scale = *scale_p;
+  const int r0 = blockIdx.y * kColRowsPerBlock;
+  const int r1 = min(r0 + kColRowsPerBlock, B_loc);
+  MS a[4] = {{-INFINITY, 0.f}, {-INFINITY, 0.f}, {-INFINITY, 0.f}, {-INFINITY, 0.f}};
+  const bool vec = (c0 + 3 < B) && ((B & 3) == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
+  for (int r = r0; r < r1; ++r) {
+    const float* x = X + static_cast<size_t>(r) * B + c0;
+    float v[4];
+    if (vec) {
+      const float4 t = __ldg(reinterpret_cast<const float4*>(x));
+      v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    } else {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) v[i] = (c0 + i < B) ? x[i] : -INFINITY;
+    }
+#pragma unroll
+    for (int i = 0; i < 4; ++i)
+      if (c0 + i < B) ms_push(a[i], scale * v[i]);
+  }
+#pragma unroll
+  for (int i = 0; i < 4; ++i)
+    if (c0 + i < B) {
+      pmax[static_cast<size_t>(blockIdx.y) * B + c0 + i] = a[i].m;
+      psum[static_cast<size_t>(blockIdx.y) * B + c0 + i] = a[i].s;
+    }
+}
+__global__ void infonce_col_combine_kernel(const float* __restrict__ pmax, const float* __restrict__ psum, int nblk,
+                                           int B, float* __restrict__ col_max, float* __restrict__ col_sum) {
+  const int c = blockIdx.x * blockDim.x + threadIdx.x;
+  if (c >= B) return;
+  MS t{-INFINITY, 0.f};
+  for (int b = 0; b < nblk; ++b) t = ms_combine(t, MS{pmax[static_cast<size_t>(b) * B + c], psum[static_cast<size_t>(b) * B + c]});
+  col_max[c] = t.m;
+  col_sum[c] = t.s;
+}
+
+// ---- gradient: dX = coef*scale*(softmax_row + softmax_col - 2*delta); dscale += sum(coef*(...)*X) ----
+__global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const float* __restrict__ scale_p,
+                                                           const float* __restrict__ coef_p, int B_loc, int B, int row0,
+                                                           const float* __restrict__ row_lse,
+                                                           const float* __restrict__ col_lse, float* dX,
+                                                           float* __restrict__ dscale_accum) {
+  const int m = blockIdx.y;
+  const float scale = *scale_p;
+  const float coef = *coef_p / (2.f * static_cast<float>(B));
+  const float rl = row_lse[m];
+  const float* x = X + static_cast<size_t>(m) * B;
+  float* dx = dX + static_cast<size_t>(m) * B;
+  const int diag_c = row0 + m;
+  float ds = 0.f;
+  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B; c += gridDim.x * blockDim.x) {
+    const float xv = x[c];
+    const float sx = scale * xv;
+    float t = expf(sx - rl) + expf(sx - col_lse[c]);
+    if (c == diag_c) t -= 2.f;
+    t *= coef;
+    ds = fmaf(t, xv, ds);
+    dx[c] = t * scale;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
+  __shared__ float part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = ds;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+    for (int w = 0; w < (blockDim.x >> 5); ++w) t += part[w];
+    atomicAdd(dscale_accum, t);
+  }
+}
+
+size_t infonce_workspace_bytes(int B_loc, int B) {
+  const size_t nblk = (static_cast<size_t>(B_loc) + kColRowsPerBlock - 1) / kColRowsPerBlock;
+  return 2 * nblk * static_cast<size_t>(B) * sizeof(float);
+}
+
+int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse, float* col_max,
+                  float* col_sum, float* diag, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
+  if (ws_bytes < infonce_workspace_bytes(B_loc, B)) return CXL_ERR_WORKSPACE;
+  const int nblk = (B_loc + kColRowsPerBlock - 1) / kColRowsPerBlock;
+  float* pmax = reinterpret_cast<float*>(ws);
+  float* psum = pmax + static_cast<size_t>(nblk) * B;
+  infonce_row_kernel<<<B_loc, 256, 0, stream>>>(X, scale_dev, B, row0, row_lse, diag);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  dim3 g((B + 511) / 512, nblk);
+  infonce_col_partial_kernel<<<g, 128, 0, stream>>>(X, scale_dev, B_loc, B, pmax, psum);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  infonce_col_combine_kernel<<<(B + 255) / 256, 256, 0, stream>>>(pmax, psum, nblk, B, col_max, col_sum);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                 const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, cudaStream_t stream) {
+  if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
+  if (B_loc > 65535) {
+    // grid.y limit: process in slabs of rows
+    for (int r = 0; r < B_loc; r += 65535) {
+      const int nr = min(65535, B_loc - r);
+      int rc = infonce_grad(X + static_cast<size_t>(r) * B, scale_dev, coef_dev, nr, B, row0 + r, row_lse + r, col_lse,
+                            dX + static_cast<size_t>(r) * B, dscale_accum, stream);
+      if (rc != CXL_OK) return rc;
+    }
+    return CXL_OK;
+  }
+  int gx = (B + 256 * 8 - 1) / (256 * 8);
+  if (gx < 1) gx = 1;
+  dim3 g(gx, B_loc);
+  infonce_grad_kernel<<<g, 256, 0, stream>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, dX, dscale_accum);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+}  // namespace cxl

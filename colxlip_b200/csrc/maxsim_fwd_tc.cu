@@ -1,0 +1,445 @@
+// K1: fused MaxSim forward on 5th-gen tensor cores (tcgen05 + TMEM, operands fed by TMA).
+//
+// Replaces loss.py:34-44 / model.py:626-628 of the reference: the [Bt*T, D] x [D, Bi*P]
+// contraction, the max over each image's patches and the per-text token sum, without ever
+// writing the [Bt,Bi,T,P] similarity tensor.  Per (text token, image) only the argmax index
+// is stored (u8/u16) for the backward.
+//
+// Tiling: M-tile = 128 consecutive rows of the flat [Bt*T, D] text-token matrix (one TMEM lane
+// per row), N-tile = the patches of one image (or `ipt` small images, or one `part` of a large
+// image), K = D in 64-wide blocks (128 B rows, SWIZZLE_128B).  The text tile stays resident in
+// shared memory for a whole work unit while image tiles stream through a TMA ring; two 256-
+// column TMEM accumulators let the max/argmax epilogue of tile i overlap the MMAs of tile i+1.
+// Warp roles: warp 0 = TMA producer, warp 1 = MMA issuer, warp 2 = TMEM allocator,
+// warps 4..7 = epilogue (warp w reads TMEM lanes 32*(w%4)..+31).
+#include "common.cuh"
+
+namespace cxl {
+
+static constexpr int kBlockM = 128;
+static constexpr int kBlockK = 64;     // bf16 elements per 128-byte swizzled row
+static constexpr int kUmmaK = 16;
+static constexpr int kThreads = 256;
+static constexpr int kABlockBytes = kBlockM * kBlockK * 2;   // 16 KB
+static constexpr int kMaxStages = 8;
+
+struct FwdTcParams {
+  int Bt, Bi, T, P, D;
+  int rows_a;            // Bt*T
+  int num_kb;            // D / 64
+  int n_tile;            // UMMA N (multiple of 16, <= 256)
+  int ipt;               // images per N-tile (>= 1)
+  int p_stride;          // rows per image in the img matrix == column stride between images in a tile
+  int parts;             // N-tiles per image (1 unless P > 256)
+  int part_cols;         // patch columns covered by one part
+  int total_n_tiles;     // ceil(Bi / ipt) * parts
+  int tiles_per_unit;    // multiple of parts
+  int num_m_tiles;
+  int num_units;
+  int a_resident;        // 1: text tile resident in smem for the whole unit, 0: streamed with B
+  int num_stages;
+  int stage_bytes;       // bytes of one ring stage (B block, plus A block when streaming)
+  int b_block_bytes;     // n_tile * 128
+  int mean_mode;
+  int argmax_u16;
+  float* S;              // [Bt,Bi] pre-zeroed accumulator of row maxima sums
+  float* cnt;            // [Bt,Bi] pre-zeroed count of non-zero maxima (or null)
+  void* argmax;          // [Bt,Bi,T] or null
+  float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
+};
+
+struct __align__(8) FwdTcBarriers {
+  uint64_t b_full[kMaxStages];
+  uint64_t b_empty[kMaxStages];
+  uint64_t a_full;
+  uint64_t a_empty;
+  uint64_t tmem_full[2];
+  uint64_t tmem_empty[2];
+  uint32_t tmem_base;
+};
+
+__device__ __forceinline__ void scan16(const uint32_t (&v)[16], int c0, int ncols, int qoff, float& best, int& bidx) {
+  float lb = -INFINITY;
+  int lj = 0;
+  if (c0 + 16 <= ncols) {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float x = __uint_as_float(v[j]);
+      if (x > lb) { lb = x; lj = j; }
+    }
+  } else {
+#pragma unroll
+    for (int j = 0; j < 16; ++j) {
+      float x = __uint_as_float(v[j]);
+      if (c0 + j < ncols && x > lb) { lb = x; lj = j; }
+    }
+  }
+  if (lb > best) { best = lb; bidx = qoff + c0 + lj; }
+}
+
+__global__ void __launch_bounds__(kThreads, 1)
+maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                     const FwdTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  // SWIZZLE_128B operand tiles need 1024-byte alignment
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int a_bytes = p.a_resident ? p.num_kb * kABlockBytes : 0;
+  uint8_t* smem_a = smem;
+  uint8_t* smem_ring = smem + a_bytes;
+  FwdTcBarriers* bars = reinterpret_cast<FwdTcBarriers*>(smem_ring + p.num_stages * p.stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(smem_u32(&bars->b_full[s]), 1);
+      mbar_init(smem_u32(&bars->b_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&bars->a_full), 1);
+    mbar_init(smem_u32(&bars->a_empty), 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bars->tmem_full[b]), 1);
+      mbar_init(smem_u32(&bars->tmem_empty[b]), 4);   // one arrive per epilogue warp
+    }
+    fence_barrier_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 2) tmem_alloc_512(smem_u32(&bars->tmem_base));
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t a_phase = 0;
+    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      const int chunk = unit / p.num_m_tiles;
+      const int m_tile = unit - chunk * p.num_m_tiles;
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      if (p.a_resident) {
+        mbar_wait(smem_u32(&bars->a_empty), a_phase ^ 1);      // previous unit's MMAs are done with A
+        mbar_arrive_expect_tx(smem_u32(&bars->a_full), p.num_kb * kABlockBytes);
+        for (int kb = 0; kb < p.num_kb; ++kb)
+          tma_load_2d(smem_u32(smem_a + kb * kABlockBytes), &tmA, smem_u32(&bars->a_full), kb * kBlockK,
+                      m_tile * kBlockM);
+        a_phase ^= 1;
+      }
+      for (int j = j0; j < j1; ++j) {
+        const int g = j / p.parts;
+        const int part = j - g * p.parts;
+        const int row0 = g * p.ipt * p.p_stride + part * p.part_cols;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(smem_u32(&bars->b_empty[stage]), phase ^ 1);
+          uint8_t* st = smem_ring + stage * p.stage_bytes;
+          const uint32_t full = smem_u32(&bars->b_full[stage]);
+          if (p.a_resident) {
+            mbar_arrive_expect_tx(full, p.b_block_bytes);
+            tma_load_2d(smem_u32(st), &tmB, full, kb * kBlockK, row0);
+          } else {
+            mbar_arrive_expect_tx(full, p.b_block_bytes + kABlockBytes);
+            tma_load_2d(smem_u32(st), &tmA, full, kb * kBlockK, m_tile * kBlockM);
+            tma_load_2d(smem_u32(st + kABlockBytes), &tmB, full, kb * kBlockK, row0);
+          }
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0) {
+    // ===================== MMA issuer =====================
+    const uint32_t idesc = umma_idesc_bf16(kBlockM, p.n_tile);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t a_phase = 0;
+    int buf = 0;
+    uint32_t acc_phase = 0;
+    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      const int chunk = unit / p.num_m_tiles;
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      if (p.a_resident) {
+        mbar_wait(smem_u32(&bars->a_full), a_phase);
+        a_phase ^= 1;
+      }
+      for (int j = j0; j < j1; ++j) {
+        mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // epilogue drained this accumulator
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * 256;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(smem_u32(&bars->b_full[stage]), phase);
+          tc_fence_after();
+          uint8_t* st = smem_ring + stage * p.stage_bytes;
+          const uint32_t a_addr = p.a_resident ? smem_u32(smem_a + kb * kABlockBytes) : smem_u32(st);
+          const uint32_t b_addr = p.a_resident ? smem_u32(st) : smem_u32(st + kABlockBytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            const uint64_t da = umma_smem_desc_sw128(a_addr + k * kUmmaK * 2);
+            const uint64_t db = umma_smem_desc_sw128(b_addr + k * kUmmaK * 2);
+            umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0);
+          }
+          umma_commit(smem_u32(&bars->b_empty[stage]));                // frees the ring slot when MMAs retire
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(smem_u32(&bars->tmem_full[buf]));                  // accumulator ready for the epilogue
+        buf ^= 1;
+        if (buf == 0) acc_phase ^= 1;
+      }
+      if (p.a_resident) umma_commit(smem_u32(&bars->a_empty));
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue: max/argmax over patches, per-text sums =====================
+    const int quad = warp & 3;
+    const int row_in_tile = quad * 32 + lane;
+    int buf = 0;
+    uint32_t acc_phase = 0;
+    for (int unit = blockIdx.x; unit < p.num_units; unit += gridDim.x) {
+      const int chunk = unit / p.num_m_tiles;
+      const int m_tile = unit - chunk * p.num_m_tiles;
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      const int R = m_tile * kBlockM + row_in_tile;
+      const bool valid = R < p.rows_a;
+      const int m = R / p.T;
+      const int n = R - m * p.T;
+      // segmented-reduction predicates: lanes of one text are contiguous
+      uint32_t same = 0;
+#pragma unroll
+      for (int o = 0; o < 5; ++o) {
+        const int off = 1 << o;
+        const int mo = __shfl_down_sync(0xffffffffu, m, off);
+        if (lane + off < 32 && mo == m) same |= 1u << o;
+      }
+      const int m_prev = __shfl_up_sync(0xffffffffu, m, 1);
+      const bool head = valid && (lane == 0 || m_prev != m);
+      const size_t pair_base = static_cast<size_t>(m) * p.Bi;
+
+      float best = -INFINITY;
+      int bidx = 0;
+      for (int j = j0; j < j1; ++j) {
+        const int g = j / p.parts;
+        const int part = j - g * p.parts;
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), acc_phase);
+        tc_fence_after();
+        const uint32_t tbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + buf * 256;
+
+        if (p.dbg != nullptr && unit == 0 && j == j0) {
+          for (int c0 = 0; c0 < p.n_tile; c0 += 16) {
+            uint32_t v[16];
+            tmem_ld16(tbase + c0, v);
+            tmem_wait_ld16(v);
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj)
+              p.dbg[static_cast<size_t>(row_in_tile) * p.n_tile + c0 + jj] = __uint_as_float(v[jj]);
+          }
+        }
+
+        const int qoff = part * p.part_cols;
+        const int ncols = (p.parts == 1) ? p.P : min(p.part_cols, p.P - qoff);
+        const int nchunks = (ncols + 15) >> 4;
+        for (int s = 0; s < p.ipt; ++s) {
+          const int k = g * p.ipt + s;
+          if (k >= p.Bi) break;
+          if (part == 0) { best = -INFINITY; bidx = 0; }
+          const uint32_t cbase = tbase + s * p.p_stride;
+          uint32_t va[16], vb[16];
+          tmem_ld16(cbase, va);
+          for (int c = 0; c < nchunks; c += 2) {
+            tmem_wait_ld16(va);
+            if (c + 1 < nchunks) tmem_ld16(cbase + (c + 1) * 16, vb);
+            scan16(va, c * 16, ncols, qoff, best, bidx);
+            if (c + 1 < nchunks) {
+              tmem_wait_ld16(vb);
+              if (c + 2 < nchunks) tmem_ld16(cbase + (c + 2) * 16, va);
+              scan16(vb, (c + 1) * 16, ncols, qoff, best, bidx);
+            }
+          }
+          if (part == p.parts - 1) {
+            // ---- emit (row, image k): argmax byte, then per-text segmented sum of the maxima ----
+            if (valid && p.argmax != nullptr) {
+              const size_t off = (pair_base + k) * p.T + n;
+              if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
+              else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
+            }
+            float v = valid ? best : 0.f;
+            float nz = (valid && best != 0.f) ? 1.f : 0.f;
+#pragma unroll
+            for (int o = 0; o < 5; ++o) {
+              const float tv = __shfl_down_sync(0xffffffffu, v, 1 << o);
+              const float tn = __shfl_down_sync(0xffffffffu, nz, 1 << o);
+              if (same & (1u << o)) { v += tv; nz += tn; }
+            }
+            if (head) {
+              atomicAdd(p.S + pair_base + k, v);
+              if (p.cnt != nullptr) atomicAdd(p.cnt + pair_base + k, nz);
+            }
+          }
+        }
+        // all tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
+        buf ^= 1;
+        if (buf == 0) acc_phase ^= 1;
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_512(tmem_base);
+  }
+}
+
+// S <- final score: masked mean  sum / (cnt + 1e-8)   (loss.py:40-44)  or plain mean sum / T (model.py:628)
+__global__ void maxsim_finalize_kernel(float* __restrict__ S, const float* __restrict__ cnt, size_t n, float inv_T,
+                                       int mean_mode) {
+  size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x;
+  const size_t stride = static_cast<size_t>(gridDim.x) * blockDim.x;
+  for (; i < n; i += stride) {
+    const float s = S[i];
+    S[i] = (mean_mode == CXL_MEAN_MASKED) ? s / (cnt[i] + 1e-8f) : s * inv_T;
+  }
+}
+
+int launch_maxsim_finalize(float* S, const float* cnt, size_t npairs, int T, int mean_mode, cudaStream_t stream) {
+  const int fb = 256;
+  const int sms = num_sms();
+  size_t fg = (npairs + fb - 1) / fb;
+  if (fg > static_cast<size_t>(sms) * 16) fg = static_cast<size_t>(sms) * 16;
+  if (fg == 0) return CXL_OK;
+  maxsim_finalize_kernel<<<static_cast<unsigned>(fg), fb, 0, stream>>>(S, cnt, npairs, 1.0f / static_cast<float>(T),
+                                                                      mean_mode);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode_fn() {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &qres) != cudaSuccess ||
+        qres != cudaDriverEntryPointSuccess)
+      return nullptr;
+    fn = reinterpret_cast<EncodeTiledFn>(ptr);
+  }
+  return fn;
+}
+
+// [rows, D] bf16 row-major matrix, box = 64 columns x box_rows rows, 128-byte swizzle
+static int make_tmap(CUtensorMap* out, const void* base, long long rows, int D, int box_rows) {
+  EncodeTiledFn fn = get_encode_fn();
+  if (fn == nullptr) return CXL_ERR_CUDA;
+  cuuint64_t gdim[2] = {static_cast<cuuint64_t>(D), static_cast<cuuint64_t>(rows)};
+  cuuint64_t gstride[1] = {static_cast<cuuint64_t>(D) * 2};
+  cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
+    return CXL_ERR_CUDA;
+  }
+  return CXL_OK;
+}
+
+static int round_up(int x, int m) { return (x + m - 1) / m * m; }
+
+int img_row_stride(int P) { return P <= 128 ? round_up(P, 8) : P; }
+
+int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
+                  float* cnt, void* argmax, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream) {
+  if (D % kBlockK != 0 || D < kBlockK) return CXL_ERR_UNSUPPORTED;
+  if (P > 65535) return CXL_ERR_UNSUPPORTED;
+  if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
+  FwdTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
+  p.rows_a = Bt * T;
+  p.num_kb = D / kBlockK;
+  p.p_stride = img_row_stride(P);
+  if (P <= 128) {
+    p.ipt = (256 - round_up(P, 16)) / p.p_stride + 1;
+    if (p.ipt > Bi) p.ipt = Bi;
+    p.parts = 1;
+    p.part_cols = P;
+    p.n_tile = round_up((p.ipt - 1) * p.p_stride + P, 16);
+  } else if (P <= 256) {
+    p.ipt = 1; p.parts = 1; p.part_cols = P;
+    p.n_tile = round_up(P, 16);
+  } else {
+    p.ipt = 1;
+    p.parts = (P + 255) / 256;
+    p.part_cols = round_up((P + p.parts - 1) / p.parts, 16);
+    p.n_tile = p.part_cols;
+  }
+  p.total_n_tiles = ((Bi + p.ipt - 1) / p.ipt) * p.parts;
+  p.num_m_tiles = (p.rows_a + kBlockM - 1) / kBlockM;
+  p.b_block_bytes = p.n_tile * kBlockK * 2;
+
+  int dev = 0, max_smem = 0;
+  CXL_CUDA_CHECK(cudaGetDevice(&dev));
+  CXL_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const int overhead = 1024 /*alignment*/ + static_cast<int>(sizeof(FwdTcBarriers)) + 64;
+  const int b_stage = round_up(p.b_block_bytes, 1024);
+  // text tile resident if it leaves room for >= 3 ring stages; otherwise stream A with B
+  p.a_resident = 1;
+  int stages = (max_smem - overhead - p.num_kb * kABlockBytes) / b_stage;
+  if (stages < 3 || force_stream_a) {
+    p.a_resident = 0;
+    p.stage_bytes = b_stage + kABlockBytes;
+    stages = (max_smem - overhead) / p.stage_bytes;
+  } else {
+    p.stage_bytes = b_stage;
+  }
+  if (stages < 2) return CXL_ERR_UNSUPPORTED;
+  p.num_stages = stages > kMaxStages ? kMaxStages : stages;
+  const int smem_bytes = overhead + (p.a_resident ? p.num_kb * kABlockBytes : 0) + p.num_stages * p.stage_bytes;
+
+  const int sms = num_sms();
+  long long total = static_cast<long long>(p.total_n_tiles) * p.num_m_tiles;
+  long long tpu = (total + sms * 8LL - 1) / (sms * 8LL);
+  tpu = (tpu + p.num_m_tiles - 1) / p.num_m_tiles;       // n-tiles per unit so that units ~ 8 x SMs
+  if (tpu > 256) tpu = 256;
+  if (tpu < 1) tpu = 1;
+  p.tiles_per_unit = round_up(static_cast<int>(tpu), p.parts);
+  if (p.tiles_per_unit > p.total_n_tiles) p.tiles_per_unit = p.total_n_tiles;
+  const int chunks = (p.total_n_tiles + p.tiles_per_unit - 1) / p.tiles_per_unit;
+  p.num_units = chunks * p.num_m_tiles;
+  p.mean_mode = mean_mode;
+  p.argmax_u16 = P > 256;
+  p.S = S; p.cnt = cnt; p.argmax = argmax; p.dbg = dbg;
+
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap(&tmA, txt, p.rows_a, D, kBlockM);
+  if (rc != CXL_OK) return rc;
+  rc = make_tmap(&tmB, img, static_cast<long long>(Bi) * p.p_stride, D, p.n_tile);
+  if (rc != CXL_OK) return rc;
+
+  const size_t npairs = static_cast<size_t>(Bt) * Bi;
+  CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
+  if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs * sizeof(float), stream));
+
+  CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  int grid = p.num_units < sms ? p.num_units : sms;
+  if (force_grid > 0 && force_grid < grid) grid = force_grid;
+  maxsim_fwd_tc_kernel<<<grid, kThreads, smem_bytes, stream>>>(tmA, tmB, p);
+  CXL_CUDA_CHECK(cudaGetLastError());
+
+  return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);
+}
+
+}  // namespace cxl

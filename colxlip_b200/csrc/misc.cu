@@ -1,0 +1,90 @@
+// Small supporting kernels: bf16 pack/cast of token embeddings and retrieval rank search.
+#include "common.cuh"
+
+namespace cxl {
+
+// src [items, n, D] (f32 or bf16, arbitrary item/row strides, unit channel stride)
+//   -> dst bf16 [items, n_pad, D] contiguous; rows n..n_pad-1 are zero.
+template <typename T>
+__global__ void pack_bf16_kernel(const T* __restrict__ src, long long item_stride, long long row_stride, int items,
+                                 int n, int n_pad, int D, __nv_bfloat16* __restrict__ dst) {
+  const int dq = D >> 2;   // groups of 4 channels
+  const size_t total = static_cast<size_t>(items) * n_pad * dq;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const int c4 = static_cast<int>(i % dq);
+    const size_t rr = i / dq;
+    const int r = static_cast<int>(rr % n_pad);
+    const size_t it = rr / n_pad;
+    float v[4] = {0.f, 0.f, 0.f, 0.f};
+    if (r < n) {
+      const T* s = src + it * item_stride + static_cast<long long>(r) * row_stride + c4 * 4;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) v[j] = static_cast<float>(s[j]);
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
+    __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
+    uint2 o;
+    o.x = *reinterpret_cast<uint32_t*>(&lo);
+    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    *reinterpret_cast<uint2*>(dst + (rr * D + c4 * 4)) = o;
+  }
+}
+
+int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
+              int D, void* dst, cudaStream_t stream) {
+  if (D % 4 != 0 || n_pad < n || items < 0) return CXL_ERR_INVALID_ARG;
+  const size_t total = static_cast<size_t>(items) * n_pad * (D >> 2);
+  if (total == 0) return CXL_OK;
+  size_t blocks = (total + 255) / 256;
+  const size_t cap = static_cast<size_t>(num_sms()) * 32;
+  if (blocks > cap) blocks = cap;
+  if (src_dtype == CXL_DTYPE_F32)
+    pack_bf16_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+        reinterpret_cast<const float*>(src), item_stride, row_stride, items, n, n_pad, D,
+        reinterpret_cast<__nv_bfloat16*>(dst));
+  else if (src_dtype == CXL_DTYPE_BF16)
+    pack_bf16_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+        reinterpret_cast<const __nv_bfloat16*>(src), item_stride, row_stride, items, n, n_pad, D,
+        reinterpret_cast<__nv_bfloat16*>(dst));
+  else
+    return CXL_ERR_INVALID_ARG;
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+// rank of the target column in a stable descending ordering of each row (train.py:467-469):
+// #entries strictly greater + #equal entries at a lower index.
+__global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __restrict__ scores, long long row_stride,
+                                                             long long col_stride, int cols,
+                                                             const int* __restrict__ target, int* __restrict__ rank_out) {
+  const int r = blockIdx.x;
+  const float* row = scores + static_cast<long long>(r) * row_stride;
+  const int t = target[r];
+  const float tv = row[static_cast<long long>(t) * col_stride];
+  int cnt = 0;
+  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+    const float v = row[static_cast<long long>(c) * col_stride];
+    cnt += (v > tv) || (v == tv && c < t);
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
+  __shared__ int part[8];
+  if ((threadIdx.x & 31) == 0) part[threadIdx.x >> 5] = cnt;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int s = 0;
+    for (int w = 0; w < 8; ++w) s += part[w];
+    rank_out[r] = s;
+  }
+}
+
+int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
+                   const int* target, int* rank_out, cudaStream_t stream) {
+  if (rows <= 0 || cols <= 0) return CXL_ERR_INVALID_ARG;
+  rank_of_target_kernel<<<rows, 256, 0, stream>>>(scores, row_stride, col_stride, cols, target, rank_out);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+}  // namespace cxl

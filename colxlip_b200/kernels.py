@@ -1,0 +1,190 @@
+"""Torch-tensor front end of the C-ABI: allocates outputs, passes raw device pointers + stream.
+
+`CudaKernels` is the only compute backend the product has.  The autograd functions in
+`colxlip_b200.loss` take a backend object so that the *host-side* logic (sharding, collectives,
+gradient scaling) can be exercised by CPU tests with a stand-in backend that lives under tests/;
+nothing in this package falls back to CPU.
+"""
+from __future__ import annotations
+
+from typing import Optional, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import CXL_DTYPE_BF16, CXL_DTYPE_F32, CXL_MEAN_MASKED, CXL_MEAN_PLAIN, check
+
+MASKED = CXL_MEAN_MASKED
+MEAN = CXL_MEAN_PLAIN
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+def _stream() -> int:
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _require_cuda(*ts: torch.Tensor) -> torch.device:
+    dev = None
+    for t in ts:
+        if t is None:
+            continue
+        if not t.is_cuda:
+            raise RuntimeError("colxlip_b200 runs on CUDA (sm_100a) tensors only; there is no CPU fallback")
+        dev = t.device if dev is None else dev
+        if t.device != dev:
+            raise RuntimeError("colxlip_b200: all tensors must live on the same CUDA device")
+    return dev
+
+
+class CudaKernels:
+    """Thin wrappers; every method enqueues on the current CUDA stream of the tensors' device."""
+
+    name = "cuda"
+    launches = 0  # number of our kernel-launching C-ABI calls (bench.py reports it)
+
+    def __init__(self):
+        self.lib = _lib.load()
+
+    # ---- layout helpers ---------------------------------------------------------------------
+    def img_row_stride(self, P: int, prec: str) -> int:
+        return int(self.lib.cxl_img_row_stride(P)) if prec == "bf16" else P
+
+    def prepare(self, x: torch.Tensor, n_pad: int, prec: str) -> torch.Tensor:
+        """[N,n,D] features -> kernel operand: bf16 [N,n_pad,D] (tensor-core path) or fp32 [N,n,D]."""
+        dev = _require_cuda(x)
+        N, n, D = x.shape
+        x = x.detach()
+        if prec == "fp32":
+            return x.float().contiguous()
+        if x.dtype == torch.bfloat16 and x.is_contiguous() and n_pad == n:
+            return x
+        if x.dtype not in (torch.float32, torch.bfloat16):
+            x = x.float()
+        if x.stride(2) != 1:
+            x = x.contiguous()
+        out = torch.empty((N, n_pad, D), dtype=torch.bfloat16, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_pack_bf16(_ptr(x), CXL_DTYPE_F32 if x.dtype == torch.float32 else CXL_DTYPE_BF16,
+                                         x.stride(0), x.stride(1), N, n, n_pad, D, _ptr(out), _stream()),
+                  "cxl_pack_bf16")
+        CudaKernels.launches += 1
+        return out
+
+    # ---- K1 --------------------------------------------------------------------------------------
+    def maxsim_fwd(self, txt_op: torch.Tensor, img_op: torch.Tensor, T: int, P: int, prec: str, mean_mode: int,
+                   save_argmax: bool) -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor]]:
+        dev = _require_cuda(txt_op, img_op)
+        Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
+        S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
+        cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if mean_mode == MASKED else None
+        argmax = None
+        if save_argmax:
+            argmax = torch.empty((Bt, Bi, T), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D,
+                                          CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
+                                          _ptr(S), _ptr(cnt), _ptr(argmax), _stream()), "cxl_maxsim_fwd")
+        CudaKernels.launches += 2
+        return S, cnt, argmax
+
+    # ---- K2 --------------------------------------------------------------------------------------
+    def maxsim_bwd(self, txt_op, img_op, argmax, dS, cnt, gscale, T: int, P: int, prec: str, mean_mode: int,
+                   need_txt: bool = True, need_img: bool = True, k_off: int = 0, n_img: Optional[int] = None):
+        dev = _require_cuda(txt_op, img_op, argmax, dS)
+        Bt, D = txt_op.shape[0], txt_op.shape[2]
+        ld = dS.shape[1]
+        n_img = img_op.shape[0] - k_off if n_img is None else n_img
+        dS = dS.contiguous()
+        dtxt = torch.empty((Bt, T, D), dtype=torch.float32, device=dev) if need_txt else None
+        dimg = torch.empty((n_img, P, D), dtype=torch.float32, device=dev) if need_img else None
+        img_shard = img_op[k_off:k_off + n_img]
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_maxsim_bwd(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(dS), _ptr(cnt),
+                                          _ptr(gscale), Bt, n_img, T, P, D,
+                                          CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
+                                          ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
+        CudaKernels.launches += int(need_txt) + int(need_img)
+        return dtxt, dimg
+
+    # ---- K3 --------------------------------------------------------------------------------------
+    def infonce_stats(self, X: torch.Tensor, scale: torch.Tensor, row0: int):
+        dev = _require_cuda(X, scale)
+        B_loc, B = X.shape
+        row_lse = torch.empty(B_loc, dtype=torch.float32, device=dev)
+        diag = torch.empty(B_loc, dtype=torch.float32, device=dev)
+        col_max = torch.empty(B, dtype=torch.float32, device=dev)
+        col_sum = torch.empty(B, dtype=torch.float32, device=dev)
+        nbytes = int(self.lib.cxl_infonce_workspace_bytes(B_loc, B))
+        ws = torch.empty(max(nbytes, 4), dtype=torch.uint8, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_infonce_stats(_ptr(X), _ptr(scale), B_loc, B, row0, _ptr(row_lse), _ptr(col_max),
+                                             _ptr(col_sum), _ptr(diag), _ptr(ws), nbytes, _stream()),
+                  "cxl_infonce_stats")
+        CudaKernels.launches += 3
+        return row_lse, col_max, col_sum, diag
+
+    def infonce_grad(self, X, scale, coef, row0: int, row_lse, col_lse):
+        dev = _require_cuda(X, scale, coef, row_lse, col_lse)
+        B_loc, B = X.shape
+        dX = torch.empty_like(X)
+        dscale = torch.zeros(1, dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_infonce_grad(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
+                                            _ptr(col_lse), _ptr(dX), _ptr(dscale), _stream()), "cxl_infonce_grad")
+        CudaKernels.launches += 1
+        return dX, dscale
+
+    # ---- retrieval ---------------------------------------------------------------------------------
+    def rank_of_target(self, scores: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
+        """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best)."""
+        dev = _require_cuda(scores, target)
+        if scores.dtype != torch.float32:
+            scores = scores.float()
+        target = target.to(device=dev, dtype=torch.int32).contiguous()
+        R, C = scores.shape
+        out = torch.empty(R, dtype=torch.int32, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_rank_of_target(_ptr(scores), scores.stride(0), scores.stride(1), R, C, _ptr(target),
+                                              _ptr(out), _stream()), "cxl_rank_of_target")
+        CudaKernels.launches += 1
+        return out
+
+    # ---- debug / test hooks -------------------------------------------------------------------------
+    def debug_tile(self, txt_bf16: torch.Tensor, img_bf16: torch.Tensor) -> torch.Tensor:
+        """Raw accumulators of one 128 x n_tile tensor-core tile: txt [<=128, D], img [129..256, D]."""
+        dev = _require_cuda(txt_bf16, img_bf16)
+        ra, D = txt_bf16.shape
+        rb = img_bf16.shape[0]
+        n_tile = (rb + 15) // 16 * 16
+        out = torch.zeros((128, n_tile), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_debug_tile(_ptr(txt_bf16.contiguous()), _ptr(img_bf16.contiguous()), ra, rb, D, n_tile,
+                                          _ptr(out), _stream()), "cxl_debug_tile")
+        return out
+
+    def maxsim_fwd_tc_ex(self, txt_op, img_op, T, P, mean_mode, save_argmax, force_stream_a=0, force_grid=0):
+        dev = _require_cuda(txt_op, img_op)
+        Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
+        S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
+        cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
+        argmax = None
+        if save_argmax:
+            argmax = torch.empty((Bt, Bi, T), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_maxsim_fwd_tc_ex(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, mean_mode, _ptr(S),
+                                                _ptr(cnt), _ptr(argmax), force_stream_a, force_grid, _stream()),
+                  "cxl_maxsim_fwd_tc_ex")
+        return S, cnt, argmax
+
+
+_default: Optional[CudaKernels] = None
+
+
+def default_kernels() -> CudaKernels:
+    global _default
+    if _default is None:
+        _default = CudaKernels()
+    return _default

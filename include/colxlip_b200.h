@@ -1,0 +1,125 @@
+/*
+ * colxlip_b200 -- C-ABI of the B200-native MaxSim contrastive scoring + loss path.
+ *
+ * The reference (lezhang7/colxlip) has no FFI: its boundary for this path is the Python
+ * API of src/colxlip/loss.py.  The entry points below are what a binding of that API
+ * calls; each one cites the reference lines it replaces.  Conventions:
+ *   - every pointer is a DEVICE pointer unless its name ends in _host;
+ *   - no allocation inside: the caller passes outputs and workspaces;
+ *   - work is enqueued on `stream` (a cudaStream_t passed as void*), nothing synchronises;
+ *   - return value 0 = success, negative = CXL_ERR_* (see cxl_strerror); no exceptions;
+ *   - thread-compatible; two calls may not share a workspace concurrently.
+ * Layouts are row-major contiguous:  txt [Bt,T,D], img [Bi,P,D], S [Bt,Bi],
+ * argmax [Bt,Bi,T] (uint8 if P <= 256 else uint16), grads shaped like their inputs.
+ */
+#ifndef COLXLIP_B200_H_
+#define COLXLIP_B200_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define CXL_OK 0
+#define CXL_ERR_INVALID_ARG (-1)   /* bad shape / null pointer / unsupported combination   */
+#define CXL_ERR_UNSUPPORTED (-2)   /* valid request this build cannot serve (e.g. D % 64)   */
+#define CXL_ERR_CUDA (-3)          /* a CUDA runtime/driver call failed (see cxl_last_cuda_error) */
+#define CXL_ERR_NO_DEVICE (-4)     /* no sm_100 device: there is NO CPU fallback             */
+#define CXL_ERR_WORKSPACE (-5)     /* workspace too small                                   */
+
+#define CXL_DTYPE_F32 0
+#define CXL_DTYPE_BF16 1
+
+#define CXL_MEAN_MASKED 0 /* loss.py:38-44  sum / (count(max != 0) + 1e-8) */
+#define CXL_MEAN_PLAIN 1  /* model.py:628   mean over all T tokens          */
+
+const char* cxl_strerror(int code);
+const char* cxl_last_cuda_error(void);
+int cxl_version(void);
+/* 0 if the current device can run the kernels (compute capability 10.x), else CXL_ERR_NO_DEVICE. */
+int cxl_device_check(void);
+/* size in bytes of one argmax element for P patches (1 or 2). */
+int cxl_argmax_elem_bytes(int P);
+
+/*
+ * Pack/cast token embeddings for the tensor-core path: src (f32 or bf16, row stride
+ * `src_row_stride` elements between consecutive tokens, `src_item_stride` between items)
+ * -> dst bf16 [items, n_pad, D] contiguous, rows >= n zero-filled.
+ * Replaces the implicit autocast copy torch.einsum performs at loss.py:34.
+ */
+int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride,
+                  int items, int n, int n_pad, int D, void* dst, void* stream);
+
+/*
+ * MaxSim forward.  Replaces compute_colbert_similarity (loss.py:20-46) when
+ * mean_mode == CXL_MEAN_MASKED and ColXLIP.compute_colbert_similarity (model.py:611-629)
+ * when mean_mode == CXL_MEAN_PLAIN.
+ *   dtype BF16: tcgen05/TMEM tensor-core kernel fed by TMA (fp32 accumulate, max over fp32);
+ *               requires D % 64 == 0.  `img` must be laid out [Bi, p_stride, D] where
+ *               p_stride = cxl_img_row_stride(P) (== P unless P < 128, see cxl_pack_bf16).
+ *   dtype F32 : SIMT fp32 kernel (parity mode, rel <= 1e-5), img is [Bi, P, D], D % 4 == 0.
+ *   S      [Bt,Bi] f32 out (final scores).
+ *   cnt    [Bt,Bi] f32 out, count of non-zero maxima (no epsilon); may be NULL for MEAN_PLAIN.
+ *   argmax [Bt,Bi,T] out or NULL (inference: nothing saved).
+ */
+int cxl_img_row_stride(int P);
+int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype,
+                   int mean_mode, float* S, float* cnt, void* argmax, void* stream);
+
+/*
+ * MaxSim backward from the saved argmax.  Replaces autograd of loss.py:34-44
+ * (value_selecting_reduction_backward + two bmm on a one-hot dS).
+ *   dS   [Bt,Bi] f32  upstream gradient of S;  cnt as written by the forward (NULL => plain mean);
+ *   gscale_dev  optional device scalar multiplied into every gradient (may be NULL);
+ *   dtxt [Bt,T,D] f32 out (overwritten) or NULL;
+ *   dimg [Bi,P,D] f32 out (overwritten unless accumulate_img != 0) or NULL.
+ * txt/img: dtype F32 -> [.,.,D] contiguous; BF16 -> img uses row stride cxl_img_row_stride(P).
+ * Image-shard calls (multi-GPU reduce-scatter pipeline): `img`/`dimg` point at the first of Bi
+ * images of a shard, while dS / cnt / argmax keep the forward's full row of `ld_pairs` images and
+ * the shard starts at image `k_off` of that row (single call: ld_pairs = Bi, k_off = 0).
+ */
+int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
+                   const float* gscale_dev, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
+                   int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img, void* stream);
+
+/*
+ * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,
+ * columns = all B images; labels are the diagonal).  Replaces `logit_scale *` and the
+ * F.cross_entropy pairs of loss.py:252-263, 285-293.
+ * Stats pass: row log-sum-exp [B_loc] and per-rank column (max, sumexp) partials [2,B] of scale*X.
+ */
+size_t cxl_infonce_workspace_bytes(int B_loc, int B);
+int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0,
+                      float* row_lse /*[B_loc]*/, float* col_max /*[B]*/, float* col_sum /*[B]*/,
+                      float* diag /*[B_loc] scale*X[m,row0+m]*/, void* ws, size_t ws_bytes, void* stream);
+/*
+ * Gradient pass: dX[m,k] = coef * scale * (exp(scale*X - row_lse[m]) + exp(scale*X - col_lse[k]) - 2*delta)
+ * with coef = *coef_dev / (2B); dscale_partial += sum(dX/scale * X) (one float, atomically added).
+ * dX may alias X.
+ */
+int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                     const float* row_lse, const float* col_lse /*[B] global*/, float* dX, float* dscale_accum,
+                     void* stream);
+
+/*
+ * Retrieval ranking: rank of the ground-truth column in every row of a score matrix
+ * (number of entries strictly greater, ties broken by lower index first, as a stable
+ * descending argsort does).  Replaces the per-row argsort loop of train.py:467-469.
+ */
+int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
+                       const int* target /*[rows]*/, int* rank_out /*[rows]*/, void* stream);
+
+/* Test hook: tensor-core forward with scheduling overrides (force the streamed-A pipeline, cap the grid). */
+int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode,
+                         float* S, float* cnt, void* argmax, int force_stream_a, int force_grid, void* stream);
+
+/* Debug aid: raw fp32 accumulators of the first 128 x n_tile tile of the tensor-core kernel. */
+int cxl_debug_tile(const void* txt_bf16, const void* img_bf16, int rowsA, int rowsB, int D, int n_tile,
+                   float* out /*[128, n_tile]*/, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* COLXLIP_B200_H_ */
