@@ -1,0 +1,345 @@
+#!/usr/bin/env python
+"""bench.py -- MaxSim-loss fwd+bwd throughput (image-text pairs/s) on B200, one JSON line on stdout.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--workload cfg2] [--impl reference]
+
+A "step" is one ColClipLoss.forward(..., output_dict=True)["total_loss"].backward() over one
+batch of synthetic L2-normalised embeddings.  Default workload at any N is BASELINE
+config 2: ViT-B/16 shape, 196 patches x 77 tokens, D=512, GLOBAL batch 32768 (strong scaling).
+`value` is timed with inputs resident in HBM; `e2e` times the same public API call from pinned
+HOST buffers (H2D of the step's inputs + D2H of the loss inside the timed region).
+`--impl reference` times the reference's CPU algorithm (oracle port: the reference is Python and
+/root/reference does not exist on the GPU box) on the host cores, on a bounded sample.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (global B, P, T, D, description)
+    "cfg1": (64, 49, 77, 512, "cfg1 ViT-B/32 B=64 P=49 T=77 D=512"),
+    "cfg2": (32768, 196, 77, 512, "cfg2 ViT-B/16 CC3M-shape B=32768 P=196 T=77 D=512"),
+    "cfg3": (8192, 196, 320, 512, "cfg3 long-caption 5x64 tokens B=8192 P=196 T=320 D=512"),
+    "cfg5": (65536, 576, 77, 768, "cfg5 ViT-L/14@336 B=65536 P=576 T=77 D=768"),
+    "small": (2048, 196, 77, 512, "reduced B=2048 P=196 T=77 D=512 (development only)"),
+}
+METRIC = "MaxSim-loss fwd+bwd image-text pairs/sec"
+
+
+def peaks():
+    p = {"hbm_gbs": 6650.0, "bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "source": "fallback"}
+    try:
+        with open(os.path.join(ROOT, "MEASURED_PEAKS.json")) as f:
+            m = json.load(f)
+        p.update({k: m[k] for k in ("hbm_gbs", "bf16_tflops", "bf16_tflops_sustained") if k in m})
+        p["source"] = "measured"
+    except Exception:
+        pass
+    return p
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled during the timed region (B200_PROFILING.md)."""
+    Q = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.idx = gpu_index
+        self.lines = []
+        self.proc = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                                          "-lms", "200", "-i", str(self.idx)], stdout=subprocess.PIPE, text=True)
+            threading.Thread(target=self._pump, daemon=True).start()
+        except Exception:
+            self.proc = None
+
+    def _pump(self):
+        for ln in self.proc.stdout:
+            self.lines.append(ln.strip())
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        sm, mx, reasons = [], [], set()
+        for ln in self.lines:
+            f = [x.strip() for x in ln.split(",")]
+            if len(f) < 9:
+                continue
+            try:
+                sm.append(float(f[1]))
+                mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for name, v in zip(("hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"), f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def synth_local(b, P, T, D, rank, device, dtype):
+    """per-rank generator seed 1234 + rank, L2-normalised Gaussian rows."""
+    g = torch.Generator(device=device).manual_seed(1234 + rank)
+    nrm = torch.nn.functional.normalize
+
+    def mk(*shape):
+        out = torch.empty(shape, device=device, dtype=dtype)
+        chunk = max(1, (1 << 28) // (shape[-1] * (shape[1] if len(shape) == 3 else 1)))
+        for i in range(0, shape[0], chunk):     # chunked so no fp32 copy of the whole tensor is ever live
+            x = torch.randn((min(chunk, shape[0] - i),) + tuple(shape[1:]), device=device, generator=g)
+            out[i:i + chunk] = nrm(x, dim=-1).to(dtype)
+        return out
+    return mk(b, D), mk(b, D), mk(b, P, D), mk(b, T, D)
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs: the reference's algorithm (oracle port) on the host cores
+# ------------------------------------------------------------------------------------------------
+def cpu_sample_shape(workload):
+    B, P, T, D, _ = WORKLOADS[workload]
+    # the reference materialises [B,B,T,P] fp32 (x ~4 live copies): keep the sample to a few GB
+    budget = 2.5e8                       # elements of the similarity tensor
+    bs = int((budget / (T * P)) ** 0.5)
+    bs = max(16, min(B, bs // 16 * 16))
+    return bs, P, T, D
+
+
+def cpu_step_time(workload, steps, warmup):
+    """Seconds per fwd+bwd of the oracle port (fp32, all host threads) on the bounded sample."""
+    from oracle import colxlip_oracle as O
+    threads = os.cpu_count() or 1
+    torch.set_num_threads(threads)
+    bs, P, T, D = cpu_sample_shape(workload)
+    img, txt, ti, tt = O.synth_inputs(bs, P, T, D, seed=1234)
+    crit = O.ColClipLossOracle(0.5)
+    times = []
+    for it in range(warmup + steps):
+        xs = [t.clone().requires_grad_() for t in (img, txt, ti, tt)]
+        ls = torch.tensor(1 / 0.07, requires_grad=True)
+        t0 = time.perf_counter()
+        out = crit(*xs, ls, output_dict=True)
+        out["total_loss"].backward()
+        dt = time.perf_counter() - t0
+        if it >= warmup:
+            times.append(dt)
+    return sum(times) / len(times), bs, threads
+
+
+def cpu_baseline_obj(workload, steps=2, warmup=1):
+    B = WORKLOADS[workload][0]
+    t, bs, threads = cpu_step_time(workload, steps, warmup)
+    inter = bs * bs / t
+    return {"value": inter / B, "unit": "pairs/s", "cores": threads, "kind": "port",
+            "sample": (f"oracle port of loss.py ColClipLoss fwd+bwd, fp32, B={bs} of the {workload} geometry, "
+                       f"{t * 1e3:.0f} ms/step = {bs / t:.1f} pairs/s at B={bs}; value = (B_s^2/t)/B_full, i.e. the "
+                       f"pair-interaction rate {inter:.3e}/s expressed at the full global batch {B}"),
+            "interactions_per_s": inter, "sample_ms_per_step": t * 1e3}
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    B, P, T, D, desc = WORKLOADS[args.workload]
+    t, bs, threads = cpu_step_time(args.workload, args.steps, max(1, args.warmup))
+    inter = bs * bs / t
+    v = inter / B
+    cb = {"value": v, "unit": "pairs/s", "cores": threads, "kind": "port",
+          "sample": f"oracle port (reference is pure Python/torch; /root/reference is absent on the GPU box), fp32, "
+                    f"B={bs} sample of {args.workload}, {t * 1e3:.0f} ms/step; value = (B_s^2/t)/{B}",
+          "interactions_per_s": inter}
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": "pairs/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": t * 1e3, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": desc, "global_batch": B, "sample_batch": bs, "patches": P, "tokens": T, "dim": D},
+            "cpu_baseline": cb,
+            "e2e": {"value": v, "unit": "pairs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}
+    print(json.dumps(line), flush=True)
+    return 0
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def run_gpu(args):
+    import torch.distributed as dist
+    from colxlip_b200 import ColClipLoss
+    from colxlip_b200.kernels import CudaKernels, default_kernels
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; colxlip_b200 has no CPU path (use --impl reference for the CPU arm)")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    B, P, T, D, desc = WORKLOADS[args.workload]
+    assert B % world == 0
+    b = B // world
+    dtype = torch.bfloat16 if args.input_dtype == "bf16" else torch.float32
+    K = default_kernels()
+
+    img, txt, ti, tt = synth_local(b, P, T, D, rank, dev, dtype)
+    feats = [img, txt, ti, tt]
+    for x in feats:
+        x.requires_grad_()
+    ls = torch.tensor(1 / 0.07, device=dev, requires_grad=True)
+    crit = ColClipLoss(alpha=0.5, rank=rank, world_size=world, gather_with_grad=False)
+
+    def step(inputs):
+        for x in inputs:
+            x.grad = None
+        ls.grad = None
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = crit(*inputs, ls, output_dict=True)
+        out["total_loss"].backward()
+        return out["total_loss"]
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(args.warmup):
+        loss = step(feats)
+    barrier()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    l0 = CudaKernels.launches
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(args.steps):
+        loss = step(feats)
+    e1.record()
+    barrier()
+    clocks = sampler.stop()
+    launches = CudaKernels.launches - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_per_step = ms.item() / args.steps
+    loss_val = loss.item()
+
+    # ---- dominant kernel (K1, tcgen05 MaxSim forward) alone: CUDA events on the launching stream ----
+    with torch.no_grad():
+        txt_op = K.prepare(tt, T, "bf16")
+        img_op = K.prepare(ti, K.img_row_stride(P, "bf16"), "bf16")
+        if world > 1:
+            full = torch.empty((B,) + tuple(img_op.shape[1:]), dtype=img_op.dtype, device=dev)
+            dist.all_gather_into_tensor(full, img_op)
+            img_op = full
+        k1_ms = []
+        for it in range(1 + args.k1_reps):
+            a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize()
+            a0.record()
+            S, cnt, arg = K.maxsim_fwd(txt_op, img_op, T, P, "bf16", 0, True)
+            a1.record()
+            torch.cuda.synchronize()
+            if it > 0:
+                k1_ms.append(a0.elapsed_time(a1))
+            del S, cnt, arg
+        del img_op, txt_op
+    k1 = sum(k1_ms) / len(k1_ms)
+    pk = peaks()
+    flops_rank = 2.0 * b * B * T * P * D
+    ach = flops_rank / (k1 * 1e-3) / 1e12
+    roofline = {"bound": "tensor", "kernel": "maxsim_fwd_tc_kernel (K1)", "achieved": ach, "peak": pk["bf16_tflops"],
+                "unit": "TFLOP/s", "frac": ach / pk["bf16_tflops"], "traffic": None,
+                "frac_of_sustained_peak": ach / pk["bf16_tflops_sustained"], "peak_source": pk["source"],
+                "kernel_ms": k1, "note": "K1 launch incl. its S/cnt memsets and the finalize kernel, timed alone"}
+
+    # ---- end to end: pinned host buffers -> H2D -> public API -> loss D2H, every step ----
+    host = [x.detach().to("cpu").pin_memory() for x in feats]
+    h2d_bytes = sum(h.numel() * h.element_size() for h in host)
+    dev_in = [torch.empty_like(x) for x in feats]
+    loss_host = torch.empty((), dtype=torch.float32).pin_memory()
+
+    def e2e_step():
+        for d, h in zip(dev_in, host):
+            d.requires_grad_(False)
+            d.copy_(h, non_blocking=True)
+            d.requires_grad_()
+        l = step(dev_in)
+        loss_host.copy_(l.detach(), non_blocking=True)
+
+    for x in feats:
+        x.grad = None
+    e2e_step()
+    barrier()
+    n_e2e = max(1, min(args.steps, args.e2e_steps))
+    t0, t1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0.record()
+    for _ in range(n_e2e):
+        e2e_step()
+    t1.record()
+    barrier()
+    ems = torch.tensor([t0.elapsed_time(t1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+    e2e_ms = ems.item() / n_e2e
+
+    if rank == 0:
+        step_flops = 2.0 * B * B * T * P * D
+        line = {
+            "metric": METRIC, "value": B / (ms_per_step * 1e-3), "unit": "pairs/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": desc, "global_batch": B, "per_gpu_batch": b, "patches": P, "tokens": T, "dim": D,
+                       "input_dtype": args.input_dtype, "autocast": "bf16", "alpha": 0.5, "logit_scale": 1 / 0.07,
+                       "l2": "inputs (GBs) far larger than the 126 MB L2; no flush needed",
+                       "step_frac_of_bf16_peak": step_flops / (ms_per_step * 1e-3) / world / (pk["bf16_tflops"] * 1e12),
+                       "loss": loss_val},
+            "roofline": roofline,
+            "e2e": {"value": B / (e2e_ms * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": h2d_bytes,
+                    "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": n_e2e},
+            "gpu_launches": launches,
+            "clocks": clocks,
+        }
+        if world == 1 and not args.no_cpu_baseline:
+            line["cpu_baseline"] = cpu_baseline_obj(args.workload)
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--workload", default=os.environ.get("CXL_BENCH_WORKLOAD", "cfg2"), choices=sorted(WORKLOADS))
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--input-dtype", default="bf16", choices=["bf16", "fp32"])
+    ap.add_argument("--k1-reps", type=int, default=2)
+    ap.add_argument("--e2e-steps", type=int, default=2)
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        return run_reference(args)
+    return run_gpu(args)
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -1,0 +1,381 @@
+"""Drop-in mirror of the reference's loss/scoring API for the MaxSim hot path.
+
+Same names, argument meaning and error behaviour as /root/reference/src/colxlip/loss.py:
+  compute_colbert_similarity  (loss.py:20-46)
+  gather_features             (loss.py:48-92)
+  ColClipLoss                 (loss.py:184-296)
+but the arithmetic runs in hand-written sm_100a CUDA kernels behind the C-ABI of
+include/colxlip_b200.h (K1 tcgen05 MaxSim forward, K2 argmax-driven backward, K3 fused
+scale/softmax/cross-entropy).  The [Bt,Bi,T,P] similarity tensor is never materialised.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+import torch.nn as nn
+from torch.autograd.function import once_differentiable
+
+try:
+    import torch.distributed.nn
+    from torch import distributed as dist
+
+    has_distributed = True
+except ImportError:  # pragma: no cover
+    has_distributed = False
+    dist = None
+
+from .kernels import MASKED, MEAN, default_kernels
+
+# "auto": tensor-core bf16 path under autocast or for 16-bit inputs, fp32 SIMT path for fp32 inputs
+# outside autocast (what torch.einsum would do at loss.py:34).  "bf16"/"fp32" force one path.
+_PRECISION = os.environ.get("COLXLIP_B200_PRECISION", "auto")
+
+
+def set_precision(mode: str) -> None:
+    global _PRECISION
+    if mode not in ("auto", "bf16", "fp32"):
+        raise ValueError("precision must be auto|bf16|fp32")
+    _PRECISION = mode
+
+
+def get_precision() -> str:
+    return _PRECISION
+
+
+def _select_precision(*tensors: torch.Tensor) -> str:
+    D = tensors[0].shape[-1]
+    mode = _PRECISION
+    if mode == "auto":
+        autocast = torch.is_autocast_enabled("cuda") if tensors[0].is_cuda else False
+        low = all(t.dtype in (torch.bfloat16, torch.float16) for t in tensors)
+        mode = "bf16" if (autocast or low) else "fp32"
+    if mode == "bf16" and D % 64 != 0:
+        mode = "fp32"  # the tcgen05 kernel tiles D in 64-wide swizzled blocks; fp32 SIMT kernel covers the rest
+    return mode
+
+
+def _check_tokens(img: torch.Tensor, txt: torch.Tensor) -> None:
+    if img.dim() != 3 or txt.dim() != 3 or img.shape[2] != txt.shape[2]:
+        raise ValueError("expected token_image_features [Bi,P,D] and token_text_features [Bt,T,D] with equal D")
+    if min(img.shape) == 0 or min(txt.shape) == 0:
+        raise ValueError("empty token tensors are not supported")
+
+
+class _MaxSimFn(torch.autograd.Function):
+    """S[Bt,Bi] = pooled max-over-patches similarity; backward from the saved argmax (K1 + K2)."""
+
+    @staticmethod
+    def forward(ctx, img_tok, txt_tok, mean_mode, prec, kernels):
+        k = kernels
+        Bi, P, D = img_tok.shape
+        Bt, T, _ = txt_tok.shape
+        need_grad = img_tok.requires_grad or txt_tok.requires_grad
+        txt_op = k.prepare(txt_tok, T, prec)
+        img_op = k.prepare(img_tok, k.img_row_stride(P, prec), prec)
+        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, mean_mode, need_grad)
+        if need_grad:
+            ctx.save_for_backward(txt_op, img_op, argmax, cnt)
+        ctx.meta = (T, P, prec, mean_mode, k, img_tok.dtype, txt_tok.dtype)
+        return S
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, dS):
+        T, P, prec, mean_mode, k, img_dt, txt_dt = ctx.meta
+        txt_op, img_op, argmax, cnt = ctx.saved_tensors
+        need_img, need_txt = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, dS.float().contiguous(), cnt, None, T, P, prec, mean_mode,
+                                  need_txt=need_txt, need_img=need_img)
+        return (dimg.to(img_dt) if need_img else None, dtxt.to(txt_dt) if need_txt else None, None, None, None)
+
+
+def _maxsim(token_image_features, token_text_features, mean_mode, kernels=None):
+    _check_tokens(token_image_features, token_text_features)
+    k = kernels if kernels is not None else default_kernels()
+    prec = _select_precision(token_image_features, token_text_features)
+    return _MaxSimFn.apply(token_image_features, token_text_features, mean_mode, prec, k)
+
+
+def compute_colbert_similarity(token_image_features, token_text_features):
+    """Token-level late-interaction score, masked-mean variant (reference loss.py:20-46).
+
+    Args:
+        token_image_features: [batch_size_img, n_img_tokens, embed_dim]
+        token_text_features:  [batch_size_txt, n_txt_tokens, embed_dim]
+    Returns:
+        [batch_size_txt, batch_size_img] fp32: for every text token the best patch similarity,
+        summed over tokens and divided by (number of non-zero maxima + 1e-8).
+    """
+    return _maxsim(token_image_features, token_text_features, MASKED)
+
+
+def compute_colbert_similarity_mean(token_image_features, token_text_features):
+    """Plain-mean variant used for retrieval inference (reference model.py:611-629)."""
+    return _maxsim(token_image_features, token_text_features, MEAN)
+
+
+def gather_features(
+        image_features,
+        text_features,
+        local_loss=False,
+        gather_with_grad=False,
+        rank=0,
+        world_size=1,
+        use_horovod=False
+):
+    """Concatenate every rank's features along dim 0 in rank order (reference loss.py:48-92).
+
+    gather_with_grad=True : autograd-aware all_gather (backward = SUM reduce-scatter).
+    gather_with_grad=False: plain all_gather under no_grad; unless local_loss, this rank's slot is
+    replaced by the live local tensor so local gradients still flow.
+    """
+    assert has_distributed, 'torch.distributed did not import correctly, please use a PyTorch version with support.'
+    if use_horovod:
+        raise RuntimeError("horovod is not supported by colxlip_b200 (the reference asserts 'Please install horovod')")
+    if gather_with_grad:
+        all_image_features = torch.cat(torch.distributed.nn.all_gather(image_features), dim=0)
+        all_text_features = torch.cat(torch.distributed.nn.all_gather(text_features), dim=0)
+        return all_image_features, all_text_features
+    with torch.no_grad():
+        img_slots = [torch.zeros_like(image_features) for _ in range(world_size)]
+        txt_slots = [torch.zeros_like(text_features) for _ in range(world_size)]
+        dist.all_gather(img_slots, image_features.contiguous())
+        dist.all_gather(txt_slots, text_features.contiguous())
+    if not local_loss:
+        img_slots[rank] = image_features
+        txt_slots[rank] = text_features
+    return torch.cat(img_slots, dim=0), torch.cat(txt_slots, dim=0)
+
+
+# ---------------------------------------------------------------------------------------------------
+# Fused loss: rows of the B x B logit matrices are sharded over ranks, columns are global.
+# ---------------------------------------------------------------------------------------------------
+def _all_gather_cat(x: torch.Tensor, world_size: int, group) -> torch.Tensor:
+    if world_size == 1:
+        return x
+    x = x.contiguous()
+    out = torch.empty((world_size * x.shape[0],) + tuple(x.shape[1:]), dtype=x.dtype, device=x.device)
+    dist.all_gather_into_tensor(out, x, group=group)
+    return out
+
+
+def _reduce_scatter_rows(x_all: torch.Tensor, world_size: int, group) -> torch.Tensor:
+    """[W*b, ...] partial sums on every rank -> [b, ...] fully summed rows of this rank."""
+    if world_size == 1:
+        return x_all
+    b = x_all.shape[0] // world_size
+    x_all = x_all.contiguous()
+    if dist.get_backend(group) == "gloo":  # CPU test harness: gloo has no reduce_scatter
+        dist.all_reduce(x_all, group=group)
+        r = dist.get_rank(group)
+        return x_all[r * b:(r + 1) * b].clone()
+    out = torch.empty((b,) + tuple(x_all.shape[1:]), dtype=x_all.dtype, device=x_all.device)
+    dist.reduce_scatter_tensor(out, x_all, op=dist.ReduceOp.SUM, group=group)
+    return out
+
+
+def _round_like_gemm_input(x: torch.Tensor, prec: str) -> torch.Tensor:
+    """fp32 copy of the global features as the GEMM sees them (bf16-rounded on the bf16 path)."""
+    x = x.detach()
+    if prec == "bf16":
+        return x.to(torch.bfloat16).float()
+    return x.float()
+
+
+class _ColClipLossFn(torch.autograd.Function):
+    """losses[3] = (global, token, total) of ColClipLoss.forward (reference loss.py:271-296)."""
+
+    @staticmethod
+    def forward(ctx, image_features, text_features, token_image_features, token_text_features, logit_scale, cfg):
+        k = cfg["kernels"]
+        W, rank, group = cfg["world_size"], cfg["rank"], cfg.get("group")
+        alpha, prec = float(cfg["alpha"]), cfg["prec"]
+        b, P, D = token_image_features.shape
+        _, T, _ = token_text_features.shape
+        B = b * W
+        row0 = rank * b
+        dev = token_image_features.device
+
+        # K4 (forward half): all-gather of the packed bf16 image tokens + global image features
+        txt_op = k.prepare(token_text_features, T, prec)
+        img_op = _all_gather_cat(k.prepare(token_image_features, k.img_row_stride(P, prec), prec), W, group)
+        g_txt = _round_like_gemm_input(text_features, prec)
+        g_img = _all_gather_cat(_round_like_gemm_input(image_features, prec), W, group)
+
+        # K1: token-level scores of this rank's texts against all images
+        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, MASKED, True)
+        # global CLIP scores (plain library GEMM, fp32 accumulate) -- SURVEY 8 f-1
+        G = g_txt @ g_img.T
+
+        scale = logit_scale.detach().float().reshape(1).to(dev)
+        stats = []
+        for X in (G, S):
+            row_lse, col_max, col_sum, diag = k.infonce_stats(X, scale, row0)
+            col_lse = col_max + torch.log(col_sum)
+            part = row_lse.sum() - 2.0 * diag.sum()
+            if W > 1:
+                col_lse = torch.logsumexp(_all_gather_cat(col_lse.unsqueeze(0), W, group), dim=0)
+                dist.all_reduce(part, group=group)
+            loss = (part + col_lse.sum()) / (2.0 * B)
+            stats.append((row_lse, col_lse, loss))
+        loss_g, loss_t = stats[0][2], stats[1][2]
+        total = alpha * loss_g + (1.0 - alpha) * loss_t
+
+        ctx.save_for_backward(txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale,
+                              stats[0][0], stats[0][1], stats[1][0], stats[1][1])
+        ctx.cfg = cfg
+        ctx.meta = (T, P, b, row0, image_features.dtype, text_features.dtype, token_image_features.dtype,
+                    token_text_features.dtype, logit_scale.dtype, logit_scale.shape)
+        return torch.stack([loss_g, loss_t, total])
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        cfg = ctx.cfg
+        k = cfg["kernels"]
+        W, group = cfg["world_size"], cfg.get("group")
+        alpha, prec = float(cfg["alpha"]), cfg["prec"]
+        T, P, b, row0, dt_img, dt_txt, dt_timg, dt_ttxt, dt_ls, ls_shape = ctx.meta
+        (txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale, rl_g, cl_g, rl_t, cl_t) = ctx.saved_tensors
+        g = g.float()
+        coef_g = (g[0] + alpha * g[2]).reshape(1).contiguous()
+        coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
+
+        # K3 gradient pass (also yields d logit_scale partials of this rank's rows)
+        dS, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t)
+        dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, rl_g, cl_g)
+        dscale = dscale_t + dscale_g
+        if W > 1:
+            dist.all_reduce(dscale, group=group)
+
+        need = ctx.needs_input_grad
+        # K2: token gradients from the saved argmax
+        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, dS, cnt, None, T, P, prec, MASKED,
+                                              need_txt=need[3], need_img=need[2])
+        d_txt = dG @ g_img if need[1] else None
+        d_img_all = dG.T @ g_txt if need[0] else None
+
+        # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
+        # reproduces the reference's x world_size (every rank back-propagates the same full loss).
+        mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
+        dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
+        d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
+
+        def fin(x, dt):
+            if x is None:
+                return None
+            if mult != 1.0:
+                x = x * mult
+            return x.to(dt)
+
+        d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[4] else None
+        return fin(d_img, dt_img), fin(d_txt, dt_txt), fin(dimg_tok, dt_timg), fin(dtxt_tok, dt_ttxt), d_ls, None
+
+
+class ColClipLoss(nn.Module):
+    """alpha * global CLIP InfoNCE + (1 - alpha) * token-level MaxSim InfoNCE (reference loss.py:184-296).
+
+    Constructor and call signatures are the reference's; `forward` is one fused autograd node
+    (K1 -> K3 stats | K3 grad -> K2) with text rows sharded over ranks when world_size > 1.
+    """
+
+    def __init__(
+            self,
+            local_loss=False,
+            gather_with_grad=False,
+            cache_labels=False,
+            rank=0,
+            world_size=1,
+            use_horovod=False,
+            alpha=0.5,
+            **kwargs
+    ):
+        super().__init__()
+        self.local_loss = local_loss
+        self.gather_with_grad = gather_with_grad
+        self.cache_labels = cache_labels
+        self.rank = rank
+        self.world_size = world_size
+        self.use_horovod = use_horovod
+        self.alpha = alpha
+        # cache state (kept for API compatibility; the fused kernels use the implicit diagonal)
+        self.prev_num_logits = 0
+        self.labels = {}
+        self._kernels = kwargs.get("kernels", None)   # test hook: stand-in backend for CPU host-logic tests
+        self._group = kwargs.get("group", None)
+
+    def _k(self):
+        return self._kernels if self._kernels is not None else default_kernels()
+
+    def get_ground_truth(self, device, num_logits) -> torch.Tensor:
+        """arange labels, cached per device when cache_labels (reference loss.py:209-221)."""
+        if self.prev_num_logits != num_logits or device not in self.labels:
+            labels = torch.arange(num_logits, device=device, dtype=torch.long)
+            if self.world_size > 1 and self.local_loss:
+                labels = labels + num_logits * self.rank
+            if self.cache_labels:
+                self.labels[device] = labels
+                self.prev_num_logits = num_logits
+        else:
+            labels = self.labels[device]
+        return labels
+
+    def get_logits(self, image_features, text_features, token_image_features, token_text_features, logit_scale,
+                   logit_bias=None):
+        """The four materialised [B,B] logit matrices (reference loss.py:223-269)."""
+        if self.world_size > 1:
+            if self.use_horovod:
+                raise RuntimeError("horovod is not supported by colxlip_b200")
+            image_features, text_features = gather_features(
+                image_features, text_features, local_loss=self.local_loss, gather_with_grad=self.gather_with_grad,
+                rank=self.rank, world_size=self.world_size, use_horovod=False)
+            token_image_features, token_text_features = gather_features(
+                token_image_features, token_text_features, local_loss=self.local_loss,
+                gather_with_grad=self.gather_with_grad, rank=self.rank, world_size=self.world_size, use_horovod=False)
+            if self.local_loss:
+                raise NotImplementedError  # same as the reference (loss.py:246-248)
+        logits_per_image = logit_scale * image_features @ text_features.T
+        logits_per_text_token = logit_scale * _maxsim(token_image_features, token_text_features, MASKED, self._k())
+        if logit_bias is not None:
+            # the reference adds the bias in place to logits_per_image and again through its transposed
+            # view (loss.py:265-267): both global matrices end up with 2 * logit_bias
+            logits_per_image = logits_per_image + 2 * logit_bias
+        return {"logits_per_image": logits_per_image, "logits_per_text": logits_per_image.T,
+                "logits_per_image_token": logits_per_text_token.T, "logits_per_text_token": logits_per_text_token}
+
+    def forward(
+            self,
+            image_features=None,
+            text_features=None,
+            token_image_features=None,
+            token_text_features=None,
+            logit_scale=None,
+            logit_bias=None,
+            output_dict=False,
+            **kwargs,
+    ):
+        # logit_bias is accepted and ignored exactly as in the reference (loss.py:283 does not forward it)
+        if self.world_size > 1:
+            if self.use_horovod:
+                raise RuntimeError("horovod is not supported by colxlip_b200")
+            if self.local_loss:
+                raise NotImplementedError
+        _check_tokens(token_image_features, token_text_features)
+        if token_image_features.shape[0] != token_text_features.shape[0]:
+            raise ValueError("ColClipLoss needs as many texts as images (labels are the diagonal)")
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        cfg = {
+            "kernels": self._k(), "world_size": self.world_size, "rank": self.rank, "group": self._group,
+            "alpha": self.alpha, "gather_with_grad": self.gather_with_grad,
+            "prec": _select_precision(token_image_features, token_text_features),
+        }
+        losses = _ColClipLossFn.apply(image_features, text_features, token_image_features, token_text_features,
+                                      logit_scale, cfg)
+        global_contrastive_loss, token_contrastive_loss, total_loss = losses[0], losses[1], losses[2]
+        if output_dict:
+            return {"global_contrastive_loss": global_contrastive_loss,
+                    "token_contrastive_loss": token_contrastive_loss, "total_loss": total_loss}
+        return total_loss

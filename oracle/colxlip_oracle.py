@@ -45,8 +45,8 @@ def maxsim_rowmax(img_tok: torch.Tensor, txt_tok: torch.Tensor) -> Tuple[torch.T
     Bi, P, D = img_tok.shape
     Bt, T, _ = txt_tok.shape
     flat_img = img_tok.reshape(Bi * P, D)
-    mx = torch.empty(Bt, Bi, T, dtype=img_tok.dtype)
-    arg = torch.empty(Bt, Bi, T, dtype=torch.int64)
+    mx = torch.empty(Bt, Bi, T, dtype=img_tok.dtype, device=img_tok.device)
+    arg = torch.empty(Bt, Bi, T, dtype=torch.int64, device=img_tok.device)
     for m in range(Bt):
         sim = (txt_tok[m] @ flat_img.T).view(T, Bi, P)           # [T,Bi,P]
         v, i = torch.max(sim, dim=2)                              # [T,Bi]
@@ -72,7 +72,7 @@ def maxsim_scores(img_tok: torch.Tensor, txt_tok: torch.Tensor, mode: int = MASK
 def maxsim_scores_blockwise(img_tok, txt_tok, mode: int = MASKED, block: int = 64) -> torch.Tensor:
     """Same values as :func:`maxsim_scores` without the [Bt,Bi,T,P] tensor."""
     Bt, Bi = txt_tok.shape[0], img_tok.shape[0]
-    out = torch.empty(Bt, Bi, dtype=torch.float32)
+    out = torch.empty(Bt, Bi, dtype=torch.float32, device=img_tok.device)
     for m0 in range(0, Bt, block):
         for k0 in range(0, Bi, block):
             out[m0:m0 + block, k0:k0 + block] = maxsim_scores(
@@ -88,7 +88,7 @@ def top2_gap(img_tok: torch.Tensor, txt_tok: torch.Tensor) -> torch.Tensor:
     """
     Bi, P, D = img_tok.shape
     Bt, T, _ = txt_tok.shape
-    gap = torch.empty(Bt, Bi, T)
+    gap = torch.empty(Bt, Bi, T, device=img_tok.device)
     flat_img = img_tok.reshape(Bi * P, D)
     for m in range(Bt):
         sim = (txt_tok[m] @ flat_img.T).view(T, Bi, P)
@@ -102,7 +102,7 @@ def top2_gap(img_tok: torch.Tensor, txt_tok: torch.Tensor) -> torch.Tensor:
 
 def infonce_pair(logits: torch.Tensor) -> torch.Tensor:
     """(CE(rows) + CE(cols)) / 2 against the diagonal -- loss.py:285-293."""
-    labels = torch.arange(logits.shape[0])
+    labels = torch.arange(logits.shape[0], device=logits.device)
     return (F.cross_entropy(logits, labels) + F.cross_entropy(logits.T, labels)) / 2
 
 
@@ -164,7 +164,7 @@ def maxsim_closed_form_grads(img_tok, txt_tok, dS, mode: int = MASKED):
     mx, arg = maxsim_rowmax(img_tok.float(), txt_tok.float())
     Bt, Bi, T = mx.shape
     if mode == MEAN:
-        cnt = torch.full((Bt, Bi), float(T))
+        cnt = torch.full((Bt, Bi), float(T), device=img_tok.device)
     else:
         cnt = (mx != 0).float().sum(dim=2) + 1e-8
     w = dS / cnt

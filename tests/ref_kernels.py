@@ -1,0 +1,82 @@
+"""CPU stand-in for colxlip_b200.kernels.CudaKernels -- TEST INFRASTRUCTURE ONLY.
+
+Implements the same backend interface with plain torch (via the oracle) so the host-side logic of
+colxlip_b200.loss (autograd wiring, row sharding, collectives, gradient scaling) can be tested on CPU
+with gloo.  The product never imports this module.
+"""
+import torch
+
+from oracle import colxlip_oracle as O
+
+MASKED, MEAN = 0, 1
+
+
+class TorchRefKernels:
+    name = "torch-ref"
+
+    def img_row_stride(self, P, prec):
+        return P
+
+    def prepare(self, x, n_pad, prec):
+        x = x.detach()
+        if prec == "bf16":
+            return x.to(torch.bfloat16).float().contiguous()
+        return x.float().contiguous()
+
+    def maxsim_fwd(self, txt_op, img_op, T, P, prec, mean_mode, save_argmax):
+        mx, arg = O.maxsim_rowmax(img_op, txt_op)
+        if mean_mode == MASKED:
+            cnt = (mx != 0).float().sum(dim=2)
+            S = mx.sum(dim=2) / (cnt + 1e-8)
+        else:
+            cnt = None
+            S = mx.mean(dim=2)
+        return S, cnt, (arg if save_argmax else None)
+
+    def maxsim_bwd(self, txt_op, img_op, argmax, dS, cnt, gscale, T, P, prec, mean_mode, need_txt=True,
+                   need_img=True, k_off=0, n_img=None):
+        Bt, _, D = txt_op.shape
+        n_img = img_op.shape[0] - k_off if n_img is None else n_img
+        g = 1.0 if gscale is None else float(gscale)
+        sl = slice(k_off, k_off + n_img)
+        w = dS[:, sl] * g / ((cnt[:, sl] + 1e-8) if mean_mode == MASKED else float(T))     # [Bt,n]
+        arg = argmax[:, sl]                                                               # [Bt,n,T]
+        img = img_op[sl]
+        dtxt = dimg = None
+        if need_txt:
+            dtxt = torch.zeros(Bt, T, D)
+            for k in range(n_img):
+                dtxt += w[:, k, None, None] * img[k][arg[:, k]]                           # [Bt,T,D]
+        if need_img:
+            dimg = torch.zeros(n_img, P, D)
+            for k in range(n_img):
+                contrib = (w[:, k, None, None] * txt_op).reshape(Bt * T, D)
+                dimg[k].index_add_(0, arg[:, k].reshape(-1), contrib)
+        return dtxt, dimg
+
+    def infonce_stats(self, X, scale, row0):
+        Z = X * scale
+        row_lse = torch.logsumexp(Z, dim=1)
+        col_max = Z.max(dim=0).values
+        col_sum = torch.exp(Z - col_max).sum(dim=0)
+        idx = torch.arange(X.shape[0])
+        diag = Z[idx, row0 + idx]
+        return row_lse, col_max, col_sum, diag
+
+    def infonce_grad(self, X, scale, coef, row0, row_lse, col_lse):
+        B_loc, B = X.shape
+        Z = X * scale
+        t = torch.exp(Z - row_lse[:, None]) + torch.exp(Z - col_lse[None, :])
+        idx = torch.arange(B_loc)
+        t[idx, row0 + idx] -= 2.0
+        t = t * (coef / (2.0 * B))
+        return t * scale, (t * X).sum().reshape(1)
+
+    def rank_of_target(self, scores, target):
+        scores = scores.float()
+        R, C = scores.shape
+        tv = scores[torch.arange(R), target.long()]
+        cols = torch.arange(C)[None, :]
+        gt = scores > tv[:, None]
+        eq = (scores == tv[:, None]) & (cols < target.long()[:, None])
+        return (gt | eq).sum(dim=1).to(torch.int32)

@@ -1,0 +1,321 @@
+"""Parity of the CUDA path (through the C-ABI) against the oracle on a real B200.  `-m gpu`.
+
+Bars (north_star): argmax exact except where the oracle's own top-2 scores tie within tolerance;
+fp32 mode rel <= 1e-5; bf16 mode rel <= 1e-2 against the fp32 reference on the ORIGINAL inputs, and
+much tighter (fp32-accumulate level) against the oracle evaluated on the bf16-rounded inputs.
+"""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import colxlip_oracle as O
+
+pytestmark = pytest.mark.gpu
+GOLDEN = os.path.join(os.path.dirname(__file__), "golden")
+LOSS_CASES = sorted(glob.glob(os.path.join(GOLDEN, "loss_*.npz")))
+
+TIE_GAP = 2e-6      # fp32 accumulation-order noise on |sim| <= 1
+# (Bt, Bi, T, P, D)
+BF16_SHAPES = [
+    (8, 8, 7, 10, 64),       # several small images per tile (P <= 128 path)
+    (12, 12, 9, 49, 64),     # cfg-1 patch count, 4 images per tile
+    (6, 6, 77, 200, 64),     # one image per tile, T straddles 128-row tiles
+    (5, 7, 77, 196, 512),    # headline geometry (ViT-B/16), rectangular
+    (3, 4, 20, 576, 128),    # ViT-L/14@336: image split in 3 parts of 192, u16 argmax
+    (4, 3, 320, 196, 256),   # long captions: T spans several M-tiles
+    (70, 33, 1, 1, 64),      # degenerate T = P = 1 (plain dot products)
+    (2, 300, 33, 130, 64),   # many images, P just above 128
+    (9, 5, 130, 257, 64),    # P just above 256 -> two parts
+]
+
+
+@pytest.fixture(scope="module")
+def K():
+    from colxlip_b200.kernels import default_kernels
+    return default_kernels()
+
+
+def _rounded(x):
+    return x.to(torch.bfloat16).float()
+
+
+def _check_argmax(arg, img, txt, what):
+    """arg: ours [Bt,Bi,T] on CPU int64; img/txt: the exact fp32 operands the kernel saw."""
+    _, ref_arg = O.maxsim_rowmax(img, txt)
+    bad = arg != ref_arg
+    if bad.any():
+        gap = O.top2_gap(img, txt)
+        assert (gap[bad] <= TIE_GAP).all(), f"{what}: {int(bad.sum())} argmax mismatches, worst gap {gap[bad].max():.3e}"
+
+
+def test_debug_tile_raw_accumulators(K):
+    g = torch.Generator().manual_seed(0)
+    for ra, rb, D in [(128, 208, 64), (100, 256, 512), (128, 144, 768)]:
+        a = torch.randn(ra, D, generator=g).to(torch.bfloat16).cuda()
+        b = torch.randn(rb, D, generator=g).to(torch.bfloat16).cuda()
+        out = K.debug_tile(a, b)[:ra, :rb].cpu()
+        ref = a.float().cpu() @ b.float().cpu().T
+        err = (out - ref).abs().max().item()
+        assert err <= 2e-3 * max(1.0, ref.abs().max().item() / 16), (ra, rb, D, err)
+
+
+@pytest.mark.parametrize("shape", BF16_SHAPES, ids=[str(s) for s in BF16_SHAPES])
+@pytest.mark.parametrize("mode", [O.MASKED, O.MEAN])
+def test_maxsim_forward_bf16(K, shape, mode):
+    Bt, Bi, T, P, D = shape
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=100 + P, pad_text=True, Bt=Bt)
+    ti, tt = _rounded(ti), _rounded(tt)
+    txt_op = K.prepare(tt.cuda(), T, "bf16")
+    img_op = K.prepare(ti.cuda(), K.img_row_stride(P, "bf16"), "bf16")
+    S, cnt, arg = K.maxsim_fwd(txt_op, img_op, T, P, "bf16", mode, True)
+    torch.cuda.synchronize()
+    ref = O.maxsim_scores_blockwise(ti, tt, mode, block=16)
+    torch.testing.assert_close(S.cpu(), ref, rtol=1e-4, atol=2e-6)
+    _check_argmax(arg.cpu().long() & 0xFFFF, ti, tt, f"bf16 {shape}")
+    if mode == O.MASKED:
+        mx, _ = O.maxsim_rowmax(ti, tt)
+        assert torch.equal(cnt.cpu(), (mx != 0).float().sum(dim=2))
+
+
+@pytest.mark.parametrize("stream_a,grid", [(1, 0), (0, 1), (1, 3), (0, 7)])
+def test_maxsim_forward_schedules(K, stream_a, grid):
+    """Streamed-A pipeline and small persistent grids (several units per CTA, ring wrap-around)."""
+    Bt, Bi, T, P, D = 9, 40, 77, 196, 128
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=5, pad_text=True, Bt=Bt)
+    ti, tt = _rounded(ti), _rounded(tt)
+    S, cnt, arg = K.maxsim_fwd_tc_ex(K.prepare(tt.cuda(), T, "bf16"), K.prepare(ti.cuda(), P, "bf16"), T, P,
+                                     O.MASKED, True, force_stream_a=stream_a, force_grid=grid)
+    torch.cuda.synchronize()
+    torch.testing.assert_close(S.cpu(), O.maxsim_scores_blockwise(ti, tt, O.MASKED, 16), rtol=1e-4, atol=2e-6)
+    _check_argmax(arg.cpu().long(), ti, tt, "schedules")
+
+
+F32_SHAPES = [(8, 8, 7, 10, 16), (12, 12, 9, 49, 64), (6, 6, 77, 200, 20), (3, 4, 20, 576, 32), (64, 64, 77, 49, 512)]
+
+
+@pytest.mark.parametrize("shape", F32_SHAPES, ids=[str(s) for s in F32_SHAPES])
+def test_maxsim_forward_fp32(K, shape):
+    Bt, Bi, T, P, D = shape
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=7 + P, pad_text=True, Bt=Bt)
+    S, cnt, arg = K.maxsim_fwd(K.prepare(tt.cuda(), T, "fp32"), K.prepare(ti.cuda(), P, "fp32"), T, P, "fp32",
+                               O.MASKED, True)
+    torch.cuda.synchronize()
+    ref = O.maxsim_scores_blockwise(ti, tt, O.MASKED, block=16)
+    torch.testing.assert_close(S.cpu(), ref, rtol=1e-5, atol=1e-6)
+    _check_argmax(arg.cpu().long() & 0xFFFF, ti, tt, f"fp32 {shape}")
+
+
+@pytest.mark.parametrize("prec", ["bf16", "fp32"])
+@pytest.mark.parametrize("shape", [(8, 8, 7, 10, 64), (6, 5, 77, 196, 128), (3, 4, 20, 576, 64), (5, 9, 33, 49, 64)],
+                         ids=str)
+@pytest.mark.parametrize("mode", [O.MASKED, O.MEAN])
+def test_maxsim_backward(K, prec, shape, mode):
+    """K2 against the closed-form backward of the oracle on the same operands."""
+    from colxlip_b200 import loss as L
+    Bt, Bi, T, P, D = shape
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=31 + T, pad_text=True, Bt=Bt)
+    if prec == "bf16":
+        ti, tt = _rounded(ti), _rounded(tt)
+    L.set_precision(prec)
+    try:
+        xi, xt = ti.cuda().requires_grad_(), tt.cuda().requires_grad_()
+        S = L._maxsim(xi, xt, mode)
+        dS = torch.randn(Bt, Bi, generator=torch.Generator().manual_seed(1))
+        S.backward(dS.cuda())
+    finally:
+        L.set_precision("auto")
+    dtxt, dimg = O.maxsim_closed_form_grads(ti, tt, dS, mode)
+    for ours, ref, n in ((xt.grad.cpu(), dtxt, "dtxt"), (xi.grad.cpu(), dimg, "dimg")):
+        tol = 1e-5 * ref.abs().max().item()
+        assert (ours - ref).abs().max().item() <= tol, (n, (ours - ref).abs().max().item(), tol)
+
+
+def test_all_zero_text_edge_case(K):
+    """count = 0 + 1e-8: logit 0 and gradient factor 1e8 (SURVEY 7.2 edge semantics)."""
+    from colxlip_b200 import loss as L
+    _, _, ti, tt = O.synth_inputs(4, 10, 5, 64, seed=2)
+    tt = tt.clone()
+    tt[1] = 0.0
+    for prec in ("bf16", "fp32"):
+        L.set_precision(prec)
+        try:
+            xi, xt = _rounded(ti).cuda().requires_grad_(), _rounded(tt).cuda().requires_grad_()
+            S = L.compute_colbert_similarity(xi, xt)
+            S.sum().backward()
+        finally:
+            L.set_precision("auto")
+        assert torch.all(S[1] == 0)
+        dtxt, dimg = O.maxsim_closed_form_grads(_rounded(ti), _rounded(tt), torch.ones(4, 4))
+        assert (xt.grad.cpu() - dtxt).abs().max() <= 1e-5 * dtxt.abs().max()
+        assert (xi.grad.cpu() - dimg).abs().max() <= 1e-5 * dimg.abs().max()
+        assert xt.grad[1].abs().max() > 1e6   # zero tokens still receive dT through argmax = 0
+
+
+# ---------------------------------------------------------------------------------------------------
+# K3 alone
+# ---------------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("B_loc,B,row0", [(7, 7, 0), (33, 33, 0), (16, 64, 32), (300, 300, 0), (130, 1030, 900)])
+def test_infonce_kernels(K, B_loc, B, row0):
+    from tests.ref_kernels import TorchRefKernels
+    R = TorchRefKernels()
+    g = torch.Generator().manual_seed(B)
+    X = torch.rand(B_loc, B, generator=g) * 2 - 1
+    scale = torch.tensor([37.0])
+    coef = torch.tensor([0.6])
+    rl, cm, cs, dg = K.infonce_stats(X.cuda(), scale.cuda(), row0)
+    rl_r, cm_r, cs_r, dg_r = R.infonce_stats(X, scale, row0)
+    torch.testing.assert_close(rl.cpu(), rl_r, rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close((cm + torch.log(cs)).cpu(), cm_r + torch.log(cs_r), rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(dg.cpu(), dg_r, rtol=1e-6, atol=1e-6)
+    cl = cm_r + torch.log(cs_r)
+    dX, dsc = K.infonce_grad(X.cuda(), scale.cuda(), coef.cuda(), row0, rl_r.cuda(), cl.cuda())
+    dX_r, dsc_r = R.infonce_grad(X, scale, coef, row0, rl_r, cl)
+    assert (dX.cpu() - dX_r).abs().max() <= 2e-5 * dX_r.abs().max()
+    assert abs(dsc.item() - dsc_r.item()) <= 1e-4 * max(abs(dsc_r.item()), 1e-3)
+
+
+# ---------------------------------------------------------------------------------------------------
+# full ColClipLoss, golden vectors produced by the reference
+# ---------------------------------------------------------------------------------------------------
+NAMES = ["image_features", "text_features", "token_image_features", "token_text_features"]
+
+
+def _run_loss(z_inputs, scale, alpha, autocast):
+    from colxlip_b200 import ColClipLoss
+    xs = [t.clone().cuda().requires_grad_() for t in z_inputs]
+    ls = torch.tensor(scale, device="cuda", requires_grad=True)
+    crit = ColClipLoss(alpha=alpha)
+    if autocast:
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            out = crit(*xs, ls, output_dict=True)
+    else:
+        out = crit(*xs, ls, output_dict=True)
+    out["total_loss"].backward()
+    torch.cuda.synchronize()
+    return {k: v.item() for k, v in out.items()}, [x.grad.cpu() for x in xs], ls.grad.item()
+
+
+@pytest.mark.parametrize("path", LOSS_CASES, ids=[os.path.basename(p)[:-4] for p in LOSS_CASES])
+def test_loss_fp32_mode_vs_reference_golden(path):
+    """fp32 inputs, no autocast -> fp32 kernels; rel <= 1e-5 against the reference's own outputs."""
+    z = np.load(path)
+    inputs = [torch.from_numpy(z[n]) for n in NAMES]
+    losses, grads, gls = _run_loss(inputs, float(z["scale"]), float(z["alpha"]), autocast=False)
+    for k in ("global_contrastive_loss", "token_contrastive_loss", "total_loss"):
+        assert abs(losses[k] - float(z[k])) <= 1e-5 * max(1.0, abs(float(z[k]))), k
+    for g, n in zip(grads, NAMES):
+        ref = torch.from_numpy(z["g_" + n])
+        assert (g - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-9, n
+    assert abs(gls - float(z["g_logit_scale"])) <= 2e-5 * max(1e-3, abs(float(z["g_logit_scale"])))
+
+
+@pytest.mark.parametrize("path", LOSS_CASES, ids=[os.path.basename(p)[:-4] for p in LOSS_CASES])
+def test_loss_bf16_autocast_vs_reference_golden(path):
+    """fp32 inputs under bf16 autocast -> tcgen05 path.  Tight against the oracle on bf16-rounded
+    inputs (same arithmetic, fp32 accumulate); within the bf16 tolerance against the fp32 golden."""
+    z = np.load(path)
+    inputs = [torch.from_numpy(z[n]) for n in NAMES]
+    scale, alpha = float(z["scale"]), float(z["alpha"])
+    losses, grads, gls = _run_loss(inputs, scale, alpha, autocast=True)
+    r_losses, r_grads = O.loss_and_grads(*[_rounded(t) for t in inputs], scale, alpha)
+    for k in r_losses:
+        assert abs(losses[k] - r_losses[k].item()) <= 2e-5 * max(1.0, abs(r_losses[k].item())), k
+        assert abs(losses[k] - float(z[k])) <= 1e-2 * max(1.0, abs(float(z[k]))), k
+    for g, n in zip(grads, NAMES):
+        ref = r_grads[n]
+        assert (g - ref).abs().max().item() <= 5e-5 * ref.abs().max().item() + 1e-9, n
+    assert abs(gls - r_grads["logit_scale"].item()) <= 1e-4 * max(1e-3, abs(r_grads["logit_scale"].item()))
+
+
+def test_cfg1_headline(K):
+    """BASELINE config 1: B=64, P=49, T=77, D=512, fp32 -> reference total loss 4.294426 (seed 1234)."""
+    z = np.load(os.path.join(GOLDEN, "cfg1_scalars.npz"))
+    inputs = list(O.synth_inputs(64, 49, 77, 512, seed=1234))
+    losses, grads, gls = _run_loss(inputs, 1 / 0.07, 0.5, autocast=False)
+    for k in losses:
+        assert abs(losses[k] - float(z[k])) <= 1e-5 * abs(float(z[k])), k
+    _, r_grads = O.loss_and_grads(*inputs, 1 / 0.07, 0.5)
+    for g, n in zip(grads, NAMES):
+        assert (g - r_grads[n]).abs().max().item() <= 1e-5 * r_grads[n].abs().max().item(), n
+    # same shape through the tensor-core path
+    losses_b, grads_b, _ = _run_loss(inputs, 1 / 0.07, 0.5, autocast=True)
+    for k in losses_b:
+        assert abs(losses_b[k] - float(z[k])) <= 1e-2 * abs(float(z[k])), k
+    for g, n in zip(grads_b, NAMES):
+        rel = (g - r_grads[n]).norm() / r_grads[n].norm()
+        assert rel <= 1e-2, (n, rel.item())
+
+
+def test_dtype_contract_bf16_inputs():
+    """pure-bf16 features: outputs fp32 scalars, gradients come back in the inputs' dtype."""
+    from colxlip_b200 import ColClipLoss, compute_colbert_similarity
+    img, txt, ti, tt = O.synth_inputs(16, 49, 12, 64, seed=8)
+    xs = [t.to(torch.bfloat16).cuda().requires_grad_() for t in (img, txt, ti, tt)]
+    ls = torch.tensor(20.0, device="cuda", requires_grad=True)
+    out = ColClipLoss()(*xs, ls, output_dict=True)
+    out["total_loss"].backward()
+    assert out["total_loss"].dtype == torch.float32
+    assert all(x.grad.dtype == torch.bfloat16 and x.grad.shape == x.shape for x in xs)
+    S = compute_colbert_similarity(xs[2].detach(), xs[3].detach())
+    assert S.dtype == torch.float32 and S.shape == (16, 16)
+    # non-contiguous inputs are accepted
+    S2 = compute_colbert_similarity(xs[2].detach().transpose(0, 1).contiguous().transpose(0, 1), xs[3].detach())
+    assert torch.equal(S, S2)
+
+
+def test_get_logits_matches_oracle():
+    from colxlip_b200 import ColClipLoss
+    img, txt, ti, tt = O.synth_inputs(10, 20, 9, 64, seed=9)
+    out = ColClipLoss().get_logits(img.cuda(), txt.cuda(), ti.cuda(), tt.cuda(), torch.tensor(15.0, device="cuda"))
+    ref = O.ColClipLossOracle().get_logits(img, txt, ti, tt, torch.tensor(15.0))
+    for k in ref:
+        torch.testing.assert_close(out[k].cpu(), ref[k], rtol=1e-4, atol=1e-4)
+
+
+# ---------------------------------------------------------------------------------------------------
+# retrieval (BASELINE config 4 geometry, reduced count) and size-independent properties at scale
+# ---------------------------------------------------------------------------------------------------
+def test_retrieval_scores_and_recall(K):
+    from colxlip_b200 import compute_colbert_similarity_mean, compute_retrieval
+    N = 96
+    _, _, ti, tt = O.synth_inputs(N, 196, 248, 128, seed=10, Bt=N)
+    tt = tt + 0.5 * ti[:, :1].expand(-1, 248, -1)        # caption i correlates with image i
+    ti, tt = _rounded(ti), _rounded(torch.nn.functional.normalize(tt, dim=-1))
+    S = compute_colbert_similarity_mean(ti.cuda().to(torch.bfloat16), tt.cuda().to(torch.bfloat16))   # [N_txt, N_img]
+    ref = O.maxsim_scores_blockwise(ti, tt, O.MEAN, block=16)
+    torch.testing.assert_close(S.cpu(), ref, rtol=1e-4, atol=2e-6)
+    ours = compute_retrieval(S.t(), list(range(N)), [[i] for i in range(N)])
+    want = O.compute_retrieval(S.t().cpu(), list(range(N)), [[i] for i in range(N)])
+    assert ours == want
+    assert ours["text_to_image_R@1"] > 0.9
+
+
+def test_properties_at_scale(K):
+    """B=384, ViT-B/16 geometry, bf16: permutation equivariance, backward linearity, scatter checksum."""
+    from colxlip_b200 import loss as L
+    B, P, T, D = 384, 196, 77, 512
+    g = torch.Generator(device="cuda").manual_seed(3)
+    ti = torch.nn.functional.normalize(torch.randn(B, P, D, device="cuda", generator=g), dim=-1).to(torch.bfloat16)
+    tt = torch.nn.functional.normalize(torch.randn(B, T, D, device="cuda", generator=g), dim=-1).to(torch.bfloat16)
+    S = L.compute_colbert_similarity(ti, tt)
+    perm = torch.randperm(B, device="cuda", generator=g)
+    S_p = L.compute_colbert_similarity(ti[perm], tt)
+    assert torch.allclose(S[:, perm], S_p, rtol=0, atol=1e-6)
+    # spot-check a block against the oracle evaluated on the device
+    ref = O.maxsim_scores(ti[:32].float(), tt[100:132].float())
+    torch.testing.assert_close(S[100:132, :32], ref, rtol=1e-4, atol=2e-6)
+    # backward is linear in dS; sum over patches of dImg == sum over texts of w * sum_n txt (checksum of the scatter)
+    xi, xt = ti.clone().requires_grad_(), tt.clone().requires_grad_()
+    S1 = L.compute_colbert_similarity(xi, xt)
+    d1 = torch.randn(B, B, device="cuda", generator=g)
+    S1.backward(d1)
+    gi1, gt1 = xi.grad.float().clone(), xt.grad.float().clone()
+    w = d1 / 77.0                                            # no zero tokens -> cnt = T (+1e-8)
+    checksum = torch.einsum("mk,md->kd", w, tt.float().sum(dim=1))
+    got = gi1.sum(dim=1)
+    assert (got - checksum).abs().max() <= 2e-2 * checksum.abs().max()   # grads were rounded to bf16 on return
+    checksum_t = torch.einsum("mnd->m", gt1)
+    assert torch.isfinite(checksum_t).all()

@@ -1,0 +1,167 @@
+"""Host-side logic of colxlip_b200.loss on CPU with a stand-in kernel backend (no CUDA needed):
+autograd wiring, alpha/coef handling, output contract, error behaviour, and the world_size-2
+row-sharded path over gloo (SURVEY 5.8 scaling rules)."""
+import os
+import socket
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from colxlip_b200 import loss as L
+from colxlip_b200.retrieval import compute_retrieval
+from oracle import colxlip_oracle as O
+from tests.ref_kernels import TorchRefKernels
+
+
+def _inputs(B, P, T, D, seed, pad=True):
+    img, txt, ti, tt = O.synth_inputs(B, P, T, D, seed=seed, pad_text=pad)
+    return img, txt, ti, tt
+
+
+@pytest.mark.parametrize("alpha,scale", [(0.5, 1 / 0.07), (0.7, 30.0), (0.0, 5.0), (1.0, 100.0)])
+def test_single_process_matches_oracle(alpha, scale):
+    img, txt, ti, tt = _inputs(9, 11, 6, 16, 3)
+    ref_losses, ref_grads = O.loss_and_grads(img, txt, ti, tt, scale, alpha)
+    xs = [t.clone().requires_grad_() for t in (img, txt, ti, tt)]
+    ls = torch.tensor(scale, requires_grad=True)
+    crit = L.ColClipLoss(alpha=alpha, kernels=TorchRefKernels())
+    out = crit(*xs, ls, output_dict=True)
+    assert set(out) == {"global_contrastive_loss", "token_contrastive_loss", "total_loss"}
+    for k in out:
+        assert out[k].dim() == 0
+        assert abs(out[k].item() - ref_losses[k].item()) < 1e-5
+    out["total_loss"].backward()
+    names = ["image_features", "text_features", "token_image_features", "token_text_features"]
+    for x, n in zip(xs, names):
+        tol = 1e-5 * ref_grads[n].abs().max().item() + 1e-8
+        assert (x.grad - ref_grads[n]).abs().max().item() <= tol, n
+    assert abs(ls.grad.item() - ref_grads["logit_scale"].item()) <= 1e-5 * max(1e-3, abs(ref_grads["logit_scale"].item()))
+
+
+def test_individual_losses_are_differentiable():
+    img, txt, ti, tt = _inputs(6, 7, 5, 16, 4)
+    xs = [t.clone().requires_grad_() for t in (img, txt, ti, tt)]
+    out = L.ColClipLoss(alpha=0.3, kernels=TorchRefKernels())(*xs, torch.tensor(10.0), output_dict=True)
+    out["token_contrastive_loss"].backward()
+    ys = [t.clone().requires_grad_() for t in (img, txt, ti, tt)]
+    ref = O.ColClipLossOracle(0.3)(*ys, torch.tensor(10.0), output_dict=True)
+    ref["token_contrastive_loss"].backward()
+    assert xs[0].grad.abs().max() == 0 and xs[1].grad.abs().max() == 0
+    torch.testing.assert_close(xs[2].grad, ys[2].grad, rtol=1e-4, atol=1e-7)
+    torch.testing.assert_close(xs[3].grad, ys[3].grad, rtol=1e-4, atol=1e-7)
+
+
+def test_total_loss_only_and_scalar_scale():
+    img, txt, ti, tt = _inputs(5, 4, 3, 16, 5)
+    t = L.ColClipLoss(kernels=TorchRefKernels())(img, txt, ti, tt, torch.tensor(14.0))
+    assert t.dim() == 0
+    ref = O.ColClipLossOracle(0.5)(img, txt, ti, tt, torch.tensor(14.0))
+    assert abs(t.item() - ref.item()) < 1e-5
+
+
+def test_accum_freq_pattern_partial_requires_grad():
+    """train.py:176-180: cat of cached (no grad) and fresh (grad) features."""
+    img, txt, ti, tt = _inputs(8, 5, 4, 16, 6)
+    fresh = [t[:4].clone().requires_grad_() for t in (img, txt, ti, tt)]
+    cat = [torch.cat([f, t[4:]]) for f, t in zip(fresh, (img, txt, ti, tt))]
+    L.ColClipLoss(kernels=TorchRefKernels())(*cat, torch.tensor(20.0)).backward()
+    _, g = O.loss_and_grads(img, txt, ti, tt, 20.0, 0.5)
+    torch.testing.assert_close(fresh[2].grad, g["token_image_features"][:4], rtol=1e-4, atol=1e-7)
+    torch.testing.assert_close(fresh[3].grad, g["token_text_features"][:4], rtol=1e-4, atol=1e-7)
+
+
+def test_get_logits_and_bias_quirk(golden_dir):
+    z = np.load(os.path.join(golden_dir, "logits_bias_b6.npz"))
+    t = lambda k: torch.from_numpy(z[k])
+    out = L.ColClipLoss(kernels=TorchRefKernels()).get_logits(
+        t("image_features"), t("text_features"), t("token_image_features"), t("token_text_features"),
+        torch.tensor(10.0), logit_bias=torch.tensor(0.25))
+    for k in ("logits_per_image", "logits_per_text", "logits_per_text_token"):
+        torch.testing.assert_close(out[k], t(k), rtol=1e-5, atol=1e-5)
+    torch.testing.assert_close(out["logits_per_image_token"], t("logits_per_text_token").T, rtol=1e-5, atol=1e-5)
+
+
+def test_error_behaviour():
+    img, txt, ti, tt = _inputs(4, 3, 3, 16, 7)
+    with pytest.raises(NotImplementedError):
+        L.ColClipLoss(local_loss=True, world_size=2, kernels=TorchRefKernels())(img, txt, ti, tt, torch.tensor(1.0))
+    with pytest.raises(RuntimeError):
+        L.ColClipLoss(use_horovod=True, world_size=2, kernels=TorchRefKernels())(img, txt, ti, tt, torch.tensor(1.0))
+    with pytest.raises(RuntimeError):   # product backend refuses CPU tensors: no CPU fallback
+        L.compute_colbert_similarity(ti, tt)
+    crit = L.ColClipLoss(cache_labels=True)
+    lab = crit.get_ground_truth(torch.device("cpu"), 5)
+    assert lab.tolist() == [0, 1, 2, 3, 4] and crit.get_ground_truth(torch.device("cpu"), 5) is lab
+
+
+def test_compute_retrieval_matches_oracle():
+    g = torch.Generator().manual_seed(1)
+    s = torch.randn(15, 30, generator=g)
+    s[3, 7] = s[3, 9]   # a tie
+    txt2img = [i // 2 for i in range(30)]
+    img2txt = [[2 * i, 2 * i + 1] for i in range(15)]
+    ours = compute_retrieval(s, txt2img, img2txt, kernels=TorchRefKernels())
+    ref = O.compute_retrieval(s, txt2img, img2txt)
+    assert ours.keys() == ref.keys()
+    for k in ref:
+        assert abs(ours[k] - ref[k]) < 1e-9, k
+
+
+# ---------------------------------------------------------------------------------------------
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _worker(rank, world, port, gather_with_grad, q):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    torch.set_num_threads(1)
+    try:
+        b = 4
+        img, txt, ti, tt = _inputs(b * world, 6, 5, 16, 9)
+        sl = slice(rank * b, (rank + 1) * b)
+        xs = [t[sl].clone().requires_grad_() for t in (img, txt, ti, tt)]
+        ls = torch.tensor(12.0, requires_grad=True)
+        crit = L.ColClipLoss(alpha=0.4, gather_with_grad=gather_with_grad, rank=rank, world_size=world,
+                             kernels=TorchRefKernels())
+        out = crit(*xs, ls, output_dict=True)
+        out["total_loss"].backward()
+        q.put((rank, {k: v.item() for k, v in out.items()}, [x.grad.numpy().copy() for x in xs], ls.grad.item()))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("gather_with_grad", [False, True])
+def test_world2_gloo_matches_global_batch(gather_with_grad):
+    world, b = 2, 4
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, gather_with_grad, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [q.get(timeout=120) for _ in range(world)]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    img, txt, ti, tt = _inputs(b * world, 6, 5, 16, 9)
+    ref_losses, ref_grads = O.loss_and_grads(img, txt, ti, tt, 12.0, 0.4)
+    mult = O.gather_scaling(gather_with_grad, world)
+    names = ["image_features", "text_features", "token_image_features", "token_text_features"]
+    for rank, losses, grads, ls_grad in res:
+        for k in losses:   # every rank reports the global-batch loss
+            assert abs(losses[k] - ref_losses[k].item()) < 1e-5
+        sl = slice(rank * b, (rank + 1) * b)
+        for g, n in zip(grads, names):
+            ref = ref_grads[n][sl] * mult
+            g = torch.from_numpy(g)
+            assert (g - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-8, (rank, n)
+        assert abs(ls_grad - ref_grads["logit_scale"].item()) < 1e-5 * max(1e-3, abs(ref_grads["logit_scale"].item()))
