@@ -32,6 +32,7 @@ WORKLOADS = {
     "cfg2": (32768, 196, 77, 512, "cfg2 ViT-B/16 CC3M-shape B=32768 P=196 T=77 D=512"),
     "cfg3": (8192, 196, 320, 512, "cfg3 long-caption 5x64 tokens B=8192 P=196 T=320 D=512"),
     "cfg5": (65536, 576, 77, 768, "cfg5 ViT-L/14@336 B=65536 P=576 T=77 D=768"),
+    "mid": (8192, 196, 77, 512, "reduced B=8192 P=196 T=77 D=512 (development only)"),
     "small": (2048, 196, 77, 512, "reduced B=2048 P=196 T=77 D=512 (development only)"),
 }
 METRIC = "MaxSim-loss fwd+bwd image-text pairs/sec"

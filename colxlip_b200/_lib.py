@@ -28,18 +28,21 @@ SYMBOLS = {
     "cxl_version": (c_int, []),
     "cxl_device_check": (c_int, []),
     "cxl_argmax_elem_bytes": (c_int, [c_int]),
+    "cxl_argmax_ld": (c_longlong, [c_int, c_int]),
     "cxl_img_row_stride": (c_int, [c_int]),
     "cxl_pack_bf16": (c_int, [c_void_p, c_int, c_longlong, c_longlong, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cxl_maxsim_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p]),
-    "cxl_maxsim_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_void_p, c_void_p,
-                               c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
-                               c_void_p, c_void_p, c_int, c_void_p]),
+    "cxl_pair_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p, c_void_p]),
+    "cxl_maxsim_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                               c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
+    "cxl_maxsim_bwd_generic": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
+                                       c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),
     "cxl_infonce_workspace_bytes": (c_size_t, [c_int, c_int]),
     "cxl_infonce_stats": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
     "cxl_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
-                                 c_void_p, c_void_p]),
+                                 c_void_p, c_void_p, c_void_p]),
     "cxl_rank_of_target": (c_int, [c_void_p, c_longlong, c_longlong, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "cxl_maxsim_fwd_tc_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),

@@ -26,17 +26,21 @@ int num_sms() {
 
 int img_row_stride(int P);
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                  float* cnt, void* argmax, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream);
+                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid,
+                  cudaStream_t stream);
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                   float* cnt, void* argmax, cudaStream_t stream);
-int maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
-               const float* gscale, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode, int p_stride,
-               int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img, cudaStream_t stream);
+                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
+int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi,
+               int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
+               int accumulate_img, int force_generic, cudaStream_t stream);
+int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
+                 cudaStream_t stream);
 size_t infonce_workspace_bytes(int B_loc, int B);
 int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse, float* col_max,
                   float* col_sum, float* diag, void* ws, size_t ws_bytes, cudaStream_t stream);
 int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
-                 const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, cudaStream_t stream);
+                 const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                 cudaStream_t stream);
 int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
               int D, void* dst, cudaStream_t stream);
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
@@ -75,6 +79,8 @@ int cxl_device_check(void) { return device_ok(); }
 
 int cxl_argmax_elem_bytes(int P) { return P > 256 ? 2 : 1; }
 
+long long cxl_argmax_ld(int Bt, int T) { return (static_cast<long long>(Bt) * T + 15) / 16 * 16; }
+
 int cxl_img_row_stride(int P) { return img_row_stride(P); }
 
 int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride, int items,
@@ -96,24 +102,41 @@ int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int 
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
-  if (dtype == CXL_DTYPE_BF16) return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, nullptr, 0, 0, st);
+  const long long ld_arg = cxl_argmax_ld(Bt, T);
+  if (dtype == CXL_DTYPE_BF16)
+    return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0, st);
   if (dtype == CXL_DTYPE_F32)
     return maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
-                          cnt, argmax, st);
+                          cnt, argmax, ld_arg, st);
   return CXL_ERR_INVALID_ARG;
 }
 
-int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
-                   const float* gscale_dev, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode, int ld_pairs,
-                   int k_off, float* dtxt, float* dimg, int accumulate_img, void* stream) {
-  if (txt == nullptr || img == nullptr || argmax == nullptr || dS == nullptr) return CXL_ERR_INVALID_ARG;
+int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev, int mean_mode, int T, long long n,
+                     float* w, void* stream) {
+  if (dS == nullptr || w == nullptr || T <= 0) return CXL_ERR_INVALID_ARG;
+  if (mean_mode != CXL_MEAN_MASKED && mean_mode != CXL_MEAN_PLAIN) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return pair_weights(dS, cnt, gscale_dev, mean_mode, T, n, w, static_cast<cudaStream_t>(stream));
+}
+
+static int bwd_entry(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
+                     int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
+                     int force_generic, void* stream) {
+  if (txt == nullptr || img == nullptr || argmax == nullptr || w == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
   if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
-  return maxsim_bwd(txt, img, argmax, dS, cnt, gscale_dev, Bt, Bi, T, P, D, dtype, mean_mode, p_stride, ld_pairs, k_off,
-                    dtxt, dimg, accumulate_img, static_cast<cudaStream_t>(stream));
+  return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
+                    dimg, accumulate_img, force_generic, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
+                   int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
+                   void* stream) {
+  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 0, stream);
 }
 
 size_t cxl_infonce_workspace_bytes(int B_loc, int B) { return infonce_workspace_bytes(B_loc, B); }
@@ -128,11 +151,12 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
 }
 
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
-                     const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, void* stream) {
+                     const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                     void* stream) {
   if (!X || !scale_dev || !coef_dev || !row_lse || !col_lse || !dX || !dscale_accum) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, dX, dscale_accum,
+  return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX, dscale_accum,
                       static_cast<cudaStream_t>(stream));
 }
 
@@ -158,8 +182,8 @@ int cxl_debug_tile(const void* txt_bf16, const void* img_bf16, int rowsA, int ro
   float* scratch = nullptr;
   CXL_CUDA_CHECK(cudaMallocAsync(&scratch, 2 * sizeof(float), st));
   // one "text" of rowsA tokens against one "image" of rowsB patches
-  rc = maxsim_fwd_tc(txt_bf16, img_bf16, 1, 1, rowsA, rowsB, D, CXL_MEAN_PLAIN, scratch, scratch + 1, nullptr, out, 0, 0,
-                     st);
+  rc = maxsim_fwd_tc(txt_bf16, img_bf16, 1, 1, rowsA, rowsB, D, CXL_MEAN_PLAIN, scratch, scratch + 1, nullptr, 0, out, 0,
+                     0, st);
   cudaFreeAsync(scratch, st);
   return rc;
 }
@@ -170,8 +194,15 @@ int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T
   if (txt == nullptr || img == nullptr || S == nullptr) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, nullptr, force_stream_a, force_grid,
-                       static_cast<cudaStream_t>(stream));
+  return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, cxl_argmax_ld(Bt, T), nullptr,
+                       force_stream_a, force_grid, static_cast<cudaStream_t>(stream));
+}
+
+// Test hook: backward through the generic (non-streaming) kernels regardless of shape.
+int cxl_maxsim_bwd_generic(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                           int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg,
+                           int accumulate_img, void* stream) {
+  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 1, stream);
 }
 
 }  // extern "C"

@@ -103,7 +103,8 @@ __global__ void infonce_col_combine_kernel(const float* __restrict__ pmax, const
 __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const float* __restrict__ scale_p,
                                                            const float* __restrict__ coef_p, int B_loc, int B, int row0,
                                                            const float* __restrict__ row_lse,
-                                                           const float* __restrict__ col_lse, float* dX,
+                                                           const float* __restrict__ col_lse,
+                                                           const float* __restrict__ cnt, float* dX,
                                                            float* __restrict__ dscale_accum) {
   const int m = blockIdx.y;
   const float scale = *scale_p;
@@ -111,6 +112,7 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
   const float rl = row_lse[m];
   const float* x = X + static_cast<size_t>(m) * B;
   float* dx = dX + static_cast<size_t>(m) * B;
+  const float* cn = cnt ? cnt + static_cast<size_t>(m) * B : nullptr;
   const int diag_c = row0 + m;
   float ds = 0.f;
   for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B; c += gridDim.x * blockDim.x) {
@@ -120,7 +122,8 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
     if (c == diag_c) t -= 2.f;
     t *= coef;
     ds = fmaf(t, xv, ds);
-    dx[c] = t * scale;
+    const float dxv = t * scale;
+    dx[c] = cn ? dxv / (cn[c] + 1e-8f) : dxv;      // with cnt: the MaxSim pair weight  dL/dS / (cnt + 1e-8)
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);
@@ -157,14 +160,16 @@ int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int 
 }
 
 int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
-                 const float* row_lse, const float* col_lse, float* dX, float* dscale_accum, cudaStream_t stream) {
+                 const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                 cudaStream_t stream) {
   if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
   if (B_loc > 65535) {
     // grid.y limit: process in slabs of rows
     for (int r = 0; r < B_loc; r += 65535) {
       const int nr = min(65535, B_loc - r);
       int rc = infonce_grad(X + static_cast<size_t>(r) * B, scale_dev, coef_dev, nr, B, row0 + r, row_lse + r, col_lse,
-                            dX + static_cast<size_t>(r) * B, dscale_accum, stream);
+                            cnt ? cnt + static_cast<size_t>(r) * B : nullptr, dX + static_cast<size_t>(r) * B,
+                            dscale_accum, stream);
       if (rc != CXL_OK) return rc;
     }
     return CXL_OK;
@@ -172,7 +177,8 @@ int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, 
   int gx = (B + 256 * 8 - 1) / (256 * 8);
   if (gx < 1) gx = 1;
   dim3 g(gx, B_loc);
-  infonce_grad_kernel<<<g, 256, 0, stream>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, dX, dscale_accum);
+  infonce_grad_kernel<<<g, 256, 0, stream>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX,
+                                             dscale_accum);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }

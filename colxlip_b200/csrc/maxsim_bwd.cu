@@ -35,24 +35,19 @@ __device__ __forceinline__ float to_f32(__nv_bfloat16 x) { return __bfloat162flo
 struct BwdParams {
   const void* txt;      // [Bt*T, D]
   const void* img;      // [Bi*p_stride, D]
-  const void* argmax;   // [Bt,Bi,T]
-  const float* dS;      // [Bt,Bi]
-  const float* cnt;     // [Bt,Bi] or null (plain mean)
-  const float* gscale;  // device scalar or null
+  const void* argmax;   // [k_off + Bi][ld_arg] image-major
+  long long ld_arg;
+  const float* w;       // [Bt, ld_pairs] per-pair weight dL/dS / cnt (cxl_pair_weights)
   int Bt, Bi, T, P, D, p_stride;
   int ld_pairs;         // row stride (in pairs) of dS / cnt / argmax: total images of the forward
   int k_off;            // first image of this call inside that row
   int argmax_u16;
-  int mean_mode;
   float* dtxt;          // [Bt*T, D]
   float* dimg;          // [Bi*P, D]
   int accumulate_img;
 };
 
-__device__ __forceinline__ float pair_weight(const BwdParams& p, size_t pair, float g) {
-  const float d = p.dS[pair] * g;
-  return (p.mean_mode == CXL_MEAN_MASKED) ? d / (p.cnt[pair] + 1e-8f) : d / static_cast<float>(p.T);
-}
+__device__ __forceinline__ float pair_weight(const BwdParams& p, size_t pair) { return p.w[pair]; }
 __device__ __forceinline__ int load_arg(const BwdParams& p, size_t off) {
   return p.argmax_u16 ? static_cast<int>(reinterpret_cast<const uint16_t*>(p.argmax)[off])
                       : static_cast<int>(reinterpret_cast<const uint8_t*>(p.argmax)[off]);
@@ -70,7 +65,6 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dtxt_kernel(const BwdParams p)
   const bool d_ok = d < p.D;
   const int m = static_cast<int>(R / p.T);
   const int n = static_cast<int>(R - static_cast<long long>(m) * p.T);
-  const float g = p.gscale ? *p.gscale : 1.f;
   const T* img = reinterpret_cast<const T*>(p.img);
   const size_t pair0 = static_cast<size_t>(m) * p.ld_pairs + p.k_off;
 
@@ -83,8 +77,8 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dtxt_kernel(const BwdParams p)
     int qv = 0;
     float wv = 0.f;
     if (kk < p.Bi) {
-      qv = load_arg(p, (pair0 + kk) * p.T + n);
-      wv = pair_weight(p, pair0 + kk, g);
+      qv = load_arg(p, static_cast<size_t>(p.k_off + kk) * p.ld_arg + R);
+      wv = pair_weight(p, pair0 + kk);
     }
     const int cnt_k = min(32, p.Bi - k0);
 #pragma unroll 4
@@ -118,7 +112,6 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
   const int c = threadIdx.x;                 // channel within slice (blockDim.x == DS)
   const int d = blockIdx.y * DS + c;
   const bool d_ok = d < p.D;
-  const float g = p.gscale ? *p.gscale : 1.f;
   const T* txt = reinterpret_cast<const T*>(p.txt);
 
   for (int i = threadIdx.x; i < p.P * DS; i += blockDim.x) acc[i] = 0.f;
@@ -126,8 +119,8 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
 
   for (int m = 0; m < p.Bt; ++m) {
     const size_t pair = static_cast<size_t>(m) * p.ld_pairs + p.k_off + k;
-    const float w = pair_weight(p, pair, g);
-    const size_t abase = pair * p.T;
+    const float w = pair_weight(p, pair);
+    const size_t abase = static_cast<size_t>(p.k_off + k) * p.ld_arg + static_cast<size_t>(m) * p.T;
     const T* trow = txt + static_cast<size_t>(m) * p.T * p.D + d;
     for (int n0 = 0; n0 < p.T; n0 += 32) {
       const int nn = n0 + lane;
@@ -153,18 +146,28 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
   }
 }
 
-int maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
-               const float* gscale, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode, int p_stride,
-               int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img, cudaStream_t stream) {
+int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt,
+                      int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
+                      int accumulate_img, cudaStream_t stream);
+
+int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi,
+               int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
+               int accumulate_img, int force_generic, cudaStream_t stream) {
   if (ld_pairs < Bi + k_off || k_off < 0) return CXL_ERR_INVALID_ARG;
-  if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
+  if (ld_arg < static_cast<long long>(Bt) * T) return CXL_ERR_INVALID_ARG;
+  if (dtype == CXL_DTYPE_BF16 && !force_generic) {
+    // fast path: TMA-staged streaming kernels; shapes it does not cover fall through to the generic kernels
+    const int rc = maxsim_bwd_stream(txt, img, argmax, ld_arg, w, Bt, Bi, T, P, D, p_stride, ld_pairs, k_off, dtxt,
+                                     dimg, accumulate_img, stream);
+    if (rc != CXL_ERR_UNSUPPORTED) return rc;
+  }
   const int V = dtype == CXL_DTYPE_BF16 ? 8 : 4;
   if (D % V != 0) return CXL_ERR_UNSUPPORTED;
   BwdParams p;
-  p.txt = txt; p.img = img; p.argmax = argmax; p.dS = dS; p.cnt = cnt; p.gscale = gscale;
+  p.txt = txt; p.img = img; p.argmax = argmax; p.ld_arg = ld_arg; p.w = w;
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D; p.p_stride = p_stride;
   p.ld_pairs = ld_pairs; p.k_off = k_off;
-  p.argmax_u16 = P > 256; p.mean_mode = mean_mode;
+  p.argmax_u16 = P > 256;
   p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img;
 
   if (dtxt != nullptr) {

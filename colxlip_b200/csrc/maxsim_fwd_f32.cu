@@ -19,6 +19,7 @@ struct FwdF32Params {
   float* S;
   float* cnt;
   void* argmax;
+  long long ld_arg;
   int argmax_u16;
 };
 
@@ -104,8 +105,7 @@ maxsim_fwd_f32_kernel(const FwdF32Params p) {
         const int R = row0 + r;
         row_best[r] = best[i];
         if (R < p.rows_a && p.argmax != nullptr) {
-          const int m = R / p.T, n = R - m * p.T;
-          const size_t off = (static_cast<size_t>(m) * p.Bi + k) * p.T + n;
+          const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
           if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx[i]);
           else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx[i]);
         }
@@ -136,14 +136,14 @@ maxsim_fwd_f32_kernel(const FwdF32Params p) {
 int launch_maxsim_finalize(float* S, const float* cnt, size_t npairs, int T, int mean_mode, cudaStream_t stream);
 
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                   float* cnt, void* argmax, cudaStream_t stream) {
+                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream) {
   if (D % 4 != 0) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
   if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
   FwdF32Params p;
   p.txt = txt; p.img = img; p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
   p.rows_a = Bt * T;
-  p.S = S; p.cnt = cnt; p.argmax = argmax; p.argmax_u16 = P > 256;
+  p.S = S; p.cnt = cnt; p.argmax = argmax; p.ld_arg = ld_arg; p.argmax_u16 = P > 256;
   const int m_tiles = (p.rows_a + FM - 1) / FM;
   const int sms = num_sms();
   int chunks = (4 * sms + m_tiles - 1) / m_tiles;

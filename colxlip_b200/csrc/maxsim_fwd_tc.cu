@@ -44,7 +44,8 @@ struct FwdTcParams {
   int argmax_u16;
   float* S;              // [Bt,Bi] pre-zeroed accumulator of row maxima sums
   float* cnt;            // [Bt,Bi] pre-zeroed count of non-zero maxima (or null)
-  void* argmax;          // [Bt,Bi,T] or null
+  void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
+  long long ld_arg;
   float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
 };
 
@@ -205,7 +206,6 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
       const int R = m_tile * kBlockM + row_in_tile;
       const bool valid = R < p.rows_a;
       const int m = R / p.T;
-      const int n = R - m * p.T;
       // segmented-reduction predicates: lanes of one text are contiguous
       uint32_t same = 0;
 #pragma unroll
@@ -261,7 +261,7 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           if (part == p.parts - 1) {
             // ---- emit (row, image k): argmax byte, then per-text segmented sum of the maxima ----
             if (valid && p.argmax != nullptr) {
-              const size_t off = (pair_base + k) * p.T + n;
+              const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
               if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
               else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
             }
@@ -361,7 +361,7 @@ static int round_up(int x, int m) { return (x + m - 1) / m * m; }
 int img_row_stride(int P) { return P <= 128 ? round_up(P, 8) : P; }
 
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                  float* cnt, void* argmax, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream) {
+                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream) {
   if (D % kBlockK != 0 || D < kBlockK) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
   if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
@@ -421,7 +421,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   p.num_units = chunks * p.num_m_tiles;
   p.mean_mode = mean_mode;
   p.argmax_u16 = P > 256;
-  p.S = S; p.cnt = cnt; p.argmax = argmax; p.dbg = dbg;
+  p.S = S; p.cnt = cnt; p.argmax = argmax; p.ld_arg = ld_arg; p.dbg = dbg;
 
   CUtensorMap tmA, tmB;
   int rc = make_tmap(&tmA, txt, p.rows_a, D, kBlockM);

@@ -53,6 +53,32 @@ int pack_bf16(const void* src, int src_dtype, long long item_stride, long long r
   return CXL_OK;
 }
 
+// w = dS * g / (cnt + 1e-8)   (masked mean, loss.py:40-44)   or   dS * g / T   (plain mean, model.py:628)
+__global__ void pair_weights_kernel(const float* __restrict__ dS, const float* __restrict__ cnt,
+                                    const float* __restrict__ gscale, int mean_mode, float inv_T, size_t n,
+                                    float* __restrict__ w) {
+  const float g = gscale ? *gscale : 1.f;
+  for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < n;
+       i += static_cast<size_t>(gridDim.x) * blockDim.x) {
+    const float d = dS[i] * g;
+    w[i] = (mean_mode == CXL_MEAN_MASKED) ? d / (cnt[i] + 1e-8f) : d * inv_T;
+  }
+}
+
+int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
+                 cudaStream_t stream) {
+  if (n <= 0) return CXL_OK;
+  if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
+  size_t blocks = (static_cast<size_t>(n) + 255) / 256;
+  const size_t cap = static_cast<size_t>(num_sms()) * 16;
+  if (blocks > cap) blocks = cap;
+  pair_weights_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(dS, cnt, gscale, mean_mode,
+                                                                        1.0f / static_cast<float>(T),
+                                                                        static_cast<size_t>(n), w);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
 // rank of the target column in a stable descending ordering of each row (train.py:467-469):
 // #entries strictly greater + #equal entries at a lower index.
 __global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __restrict__ scores, long long row_stride,

@@ -73,6 +73,18 @@ class CudaKernels:
         CudaKernels.launches += 1
         return out
 
+    def _alloc_argmax(self, Bt: int, Bi: int, T: int, P: int, dev) -> torch.Tensor:
+        """Image-major saved argmax [Bi, cxl_argmax_ld(Bt,T)] (u8 for P <= 256, else 16-bit)."""
+        ld = int(self.lib.cxl_argmax_ld(Bt, T))
+        return torch.empty((Bi, ld), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
+
+    @staticmethod
+    def argmax_as_text_major(argmax: torch.Tensor, Bt: int, T: int) -> torch.Tensor:
+        """[Bi, ld] image-major -> [Bt, Bi, T] int64 (for checks against the oracle)."""
+        Bi = argmax.shape[0]
+        a = argmax[:, :Bt * T].reshape(Bi, Bt, T).permute(1, 0, 2)
+        return a.long() & 0xFFFF
+
     # ---- K1 --------------------------------------------------------------------------------------
     def maxsim_fwd(self, txt_op: torch.Tensor, img_op: torch.Tensor, T: int, P: int, prec: str, mean_mode: int,
                    save_argmax: bool) -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor]]:
@@ -80,9 +92,7 @@ class CudaKernels:
         Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
         S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
         cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if mean_mode == MASKED else None
-        argmax = None
-        if save_argmax:
-            argmax = torch.empty((Bt, Bi, T), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
+        argmax = self._alloc_argmax(Bt, Bi, T, P, dev) if save_argmax else None
         with torch.cuda.device(dev):
             check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D,
                                           CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
@@ -91,21 +101,34 @@ class CudaKernels:
         return S, cnt, argmax
 
     # ---- K2 --------------------------------------------------------------------------------------
-    def maxsim_bwd(self, txt_op, img_op, argmax, dS, cnt, gscale, T: int, P: int, prec: str, mean_mode: int,
-                   need_txt: bool = True, need_img: bool = True, k_off: int = 0, n_img: Optional[int] = None):
-        dev = _require_cuda(txt_op, img_op, argmax, dS)
+    def pair_weights(self, dS: torch.Tensor, cnt: Optional[torch.Tensor], T: int, mean_mode: int) -> torch.Tensor:
+        """w = dS / (cnt + 1e-8) (masked mean) or dS / T (plain mean), fp32 [Bt,Bi]."""
+        dev = _require_cuda(dS, cnt)
+        dS = dS.float().contiguous()
+        w = torch.empty_like(dS)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_pair_weights(_ptr(dS), _ptr(cnt), None, mean_mode, T, dS.numel(), _ptr(w), _stream()),
+                  "cxl_pair_weights")
+        CudaKernels.launches += 1
+        return w
+
+    def maxsim_bwd(self, txt_op, img_op, argmax, w, T: int, P: int, prec: str,
+                   need_txt: bool = True, need_img: bool = True, k_off: int = 0, n_img: Optional[int] = None,
+                   generic: bool = False):
+        """w: [Bt, ld_pairs] fp32 pair weights (pair_weights / infonce_grad with cnt)."""
+        dev = _require_cuda(txt_op, img_op, argmax, w)
         Bt, D = txt_op.shape[0], txt_op.shape[2]
-        ld = dS.shape[1]
+        ld = w.shape[1]
         n_img = img_op.shape[0] - k_off if n_img is None else n_img
-        dS = dS.contiguous()
+        assert w.is_contiguous() and w.dtype == torch.float32
         dtxt = torch.empty((Bt, T, D), dtype=torch.float32, device=dev) if need_txt else None
         dimg = torch.empty((n_img, P, D), dtype=torch.float32, device=dev) if need_img else None
         img_shard = img_op[k_off:k_off + n_img]
         with torch.cuda.device(dev):
-            check(self.lib.cxl_maxsim_bwd(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(dS), _ptr(cnt),
-                                          _ptr(gscale), Bt, n_img, T, P, D,
-                                          CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
-                                          ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
+            fn = self.lib.cxl_maxsim_bwd_generic if generic else self.lib.cxl_maxsim_bwd
+            check(fn(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img, T, P, D,
+                     CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32,
+                     ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
         CudaKernels.launches += int(need_txt) + int(need_img)
         return dtxt, dimg
 
@@ -126,14 +149,16 @@ class CudaKernels:
         CudaKernels.launches += 3
         return row_lse, col_max, col_sum, diag
 
-    def infonce_grad(self, X, scale, coef, row0: int, row_lse, col_lse):
+    def infonce_grad(self, X, scale, coef, row0: int, row_lse, col_lse, cnt=None, out=None):
+        """dX (or, with cnt, the MaxSim pair weights dX / (cnt + 1e-8)); `out` may alias X."""
         dev = _require_cuda(X, scale, coef, row_lse, col_lse)
         B_loc, B = X.shape
-        dX = torch.empty_like(X)
+        dX = torch.empty_like(X) if out is None else out
         dscale = torch.zeros(1, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
             check(self.lib.cxl_infonce_grad(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
-                                            _ptr(col_lse), _ptr(dX), _ptr(dscale), _stream()), "cxl_infonce_grad")
+                                            _ptr(col_lse), _ptr(cnt), _ptr(dX), _ptr(dscale), _stream()),
+                  "cxl_infonce_grad")
         CudaKernels.launches += 1
         return dX, dscale
 
@@ -170,9 +195,7 @@ class CudaKernels:
         Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
         S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
         cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
-        argmax = None
-        if save_argmax:
-            argmax = torch.empty((Bt, Bi, T), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
+        argmax = self._alloc_argmax(Bt, Bi, T, P, dev) if save_argmax else None
         with torch.cuda.device(dev):
             check(self.lib.cxl_maxsim_fwd_tc_ex(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, mean_mode, _ptr(S),
                                                 _ptr(cnt), _ptr(argmax), force_stream_a, force_grid, _stream()),

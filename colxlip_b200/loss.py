@@ -86,8 +86,8 @@ class _MaxSimFn(torch.autograd.Function):
         T, P, prec, mean_mode, k, img_dt, txt_dt = ctx.meta
         txt_op, img_op, argmax, cnt = ctx.saved_tensors
         need_img, need_txt = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
-        dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, dS.float().contiguous(), cnt, None, T, P, prec, mean_mode,
-                                  need_txt=need_txt, need_img=need_img)
+        w = k.pair_weights(dS, cnt, T, mean_mode)
+        dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=need_txt, need_img=need_img)
         return (dimg.to(img_dt) if need_img else None, dtxt.to(txt_dt) if need_txt else None, None, None, None)
 
 
@@ -189,6 +189,13 @@ class _ColClipLossFn(torch.autograd.Function):
 
     @staticmethod
     def forward(ctx, image_features, text_features, token_image_features, token_text_features, logit_scale, cfg):
+        # precision is decided by cfg["prec"]; the few torch ops in here must not be re-cast by an ambient autocast
+        with torch.autocast(token_image_features.device.type, enabled=False):
+            return _ColClipLossFn._forward(ctx, image_features, text_features, token_image_features,
+                                           token_text_features, logit_scale, cfg)
+
+    @staticmethod
+    def _forward(ctx, image_features, text_features, token_image_features, token_text_features, logit_scale, cfg):
         k = cfg["kernels"]
         W, rank, group = cfg["world_size"], cfg["rank"], cfg.get("group")
         alpha, prec = float(cfg["alpha"]), cfg["prec"]
@@ -244,7 +251,7 @@ class _ColClipLossFn(torch.autograd.Function):
         coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
 
         # K3 gradient pass (also yields d logit_scale partials of this rank's rows)
-        dS, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t)
+        w, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t, cnt=cnt)   # pair weights dL/dS / cnt
         dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, rl_g, cl_g)
         dscale = dscale_t + dscale_g
         if W > 1:
@@ -252,7 +259,7 @@ class _ColClipLossFn(torch.autograd.Function):
 
         need = ctx.needs_input_grad
         # K2: token gradients from the saved argmax
-        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, dS, cnt, None, T, P, prec, MASKED,
+        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
                                               need_txt=need[3], need_img=need[2])
         d_txt = dG @ g_img if need[1] else None
         d_img_all = dG.T @ g_txt if need[0] else None

@@ -9,8 +9,11 @@
  *   - work is enqueued on `stream` (a cudaStream_t passed as void*), nothing synchronises;
  *   - return value 0 = success, negative = CXL_ERR_* (see cxl_strerror); no exceptions;
  *   - thread-compatible; two calls may not share a workspace concurrently.
- * Layouts are row-major contiguous:  txt [Bt,T,D], img [Bi,P,D], S [Bt,Bi],
- * argmax [Bt,Bi,T] (uint8 if P <= 256 else uint16), grads shaped like their inputs.
+ * Layouts are row-major contiguous:  txt [Bt,T,D], img [Bi,P,D], S [Bt,Bi], grads shaped like
+ * their inputs.  The saved argmax is IMAGE-major: argmax[k][r] = best patch of image k for the
+ * flat text-token row r = m*T + n, row pitch cxl_argmax_ld(Bt,T) elements (Bt*T rounded up to
+ * 16), element uint8 if P <= 256 else uint16 -- so one image's items are one contiguous stream
+ * for the backward and a row tile's items are a contiguous run per image.
  */
 #ifndef COLXLIP_B200_H_
 #define COLXLIP_B200_H_
@@ -42,6 +45,8 @@ int cxl_version(void);
 int cxl_device_check(void);
 /* size in bytes of one argmax element for P patches (1 or 2). */
 int cxl_argmax_elem_bytes(int P);
+/* row pitch (elements) of the image-major argmax buffer: total elements = Bi * cxl_argmax_ld(Bt, T). */
+long long cxl_argmax_ld(int Bt, int T);
 
 /*
  * Pack/cast token embeddings for the tensor-core path: src (f32 or bf16, row stride
@@ -62,27 +67,37 @@ int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, lon
  *   dtype F32 : SIMT fp32 kernel (parity mode, rel <= 1e-5), img is [Bi, P, D], D % 4 == 0.
  *   S      [Bt,Bi] f32 out (final scores).
  *   cnt    [Bt,Bi] f32 out, count of non-zero maxima (no epsilon); may be NULL for MEAN_PLAIN.
- *   argmax [Bt,Bi,T] out or NULL (inference: nothing saved).
+ *   argmax [Bi][cxl_argmax_ld(Bt,T)] out or NULL (inference: nothing saved).
  */
 int cxl_img_row_stride(int P);
 int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype,
                    int mean_mode, float* S, float* cnt, void* argmax, void* stream);
 
 /*
+ * Per-pair backward weights  w[m,k] = dS[m,k] * g / (cnt[m,k] + 1e-8)   (CXL_MEAN_MASKED, loss.py:40-44)
+ *                                    = dS[m,k] * g / T                   (CXL_MEAN_PLAIN,  model.py:628)
+ * over n = Bt*Bi contiguous pairs; gscale_dev is an optional device scalar g; w may alias dS.
+ * (cxl_infonce_grad writes w directly when given cnt, so the fused loss never calls this.)
+ */
+int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev, int mean_mode, int T, long long n,
+                     float* w, void* stream);
+
+/*
  * MaxSim backward from the saved argmax.  Replaces autograd of loss.py:34-44
- * (value_selecting_reduction_backward + two bmm on a one-hot dS).
- *   dS   [Bt,Bi] f32  upstream gradient of S;  cnt as written by the forward (NULL => plain mean);
- *   gscale_dev  optional device scalar multiplied into every gradient (may be NULL);
- *   dtxt [Bt,T,D] f32 out (overwritten) or NULL;
- *   dimg [Bi,P,D] f32 out (overwritten unless accumulate_img != 0) or NULL.
+ * (value_selecting_reduction_backward + two bmm on a one-hot dS):
+ *   dtxt[m,n,:] = sum_k w[m,k] * img[k, argmax(m,k,n), :]      [Bt,T,D] f32 out (overwritten) or NULL
+ *   dimg[k,q,:] = sum_{m,n: argmax(m,k,n)=q} w[m,k] * txt[m,n,:]  [Bi,P,D] f32 out (overwritten unless
+ *                                                                accumulate_img != 0) or NULL
+ *   w [Bt, ld_pairs] f32 pair weights (cxl_pair_weights / cxl_infonce_grad).
  * txt/img: dtype F32 -> [.,.,D] contiguous; BF16 -> img uses row stride cxl_img_row_stride(P).
  * Image-shard calls (multi-GPU reduce-scatter pipeline): `img`/`dimg` point at the first of Bi
- * images of a shard, while dS / cnt / argmax keep the forward's full row of `ld_pairs` images and
- * the shard starts at image `k_off` of that row (single call: ld_pairs = Bi, k_off = 0).
+ * images of a shard, while w / argmax are the forward's full buffers over `ld_pairs` images and
+ * the shard starts at image `k_off` of them (single call: ld_pairs = Bi, k_off = 0).
+ * bf16 shapes with D % 128 == 0 and T >= 8 run the TMA-staged streaming kernels; the rest a generic kernel.
  */
-int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* dS, const float* cnt,
-                   const float* gscale_dev, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
-                   int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img, void* stream);
+int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
+                   int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
+                   void* stream);
 
 /*
  * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,
@@ -97,11 +112,12 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
 /*
  * Gradient pass: dX[m,k] = coef * scale * (exp(scale*X - row_lse[m]) + exp(scale*X - col_lse[k]) - 2*delta)
  * with coef = *coef_dev / (2B); dscale_partial += sum(dX/scale * X) (one float, atomically added).
+ * If cnt != NULL (token logits) the output is the MaxSim pair weight dX / (cnt + 1e-8) instead of dX.
  * dX may alias X.
  */
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
-                     const float* row_lse, const float* col_lse /*[B] global*/, float* dX, float* dscale_accum,
-                     void* stream);
+                     const float* row_lse, const float* col_lse /*[B] global*/, const float* cnt /*[B_loc,B] or NULL*/,
+                     float* dX, float* dscale_accum, void* stream);
 
 /*
  * Retrieval ranking: rank of the ground-truth column in every row of a score matrix
@@ -114,6 +130,11 @@ int cxl_rank_of_target(const float* scores, long long row_stride, long long col_
 /* Test hook: tensor-core forward with scheduling overrides (force the streamed-A pipeline, cap the grid). */
 int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode,
                          float* S, float* cnt, void* argmax, int force_stream_a, int force_grid, void* stream);
+
+/* Test hook: cxl_maxsim_bwd through the generic (non-streaming) kernels regardless of shape. */
+int cxl_maxsim_bwd_generic(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                           int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg,
+                           int accumulate_img, void* stream);
 
 /* Debug aid: raw fp32 accumulators of the first 128 x n_tile tile of the tensor-core kernel. */
 int cxl_debug_tile(const void* txt_bf16, const void* img_bf16, int rowsA, int rowsB, int D, int n_tile,

@@ -33,13 +33,15 @@ class TorchRefKernels:
             S = mx.mean(dim=2)
         return S, cnt, (arg if save_argmax else None)
 
-    def maxsim_bwd(self, txt_op, img_op, argmax, dS, cnt, gscale, T, P, prec, mean_mode, need_txt=True,
-                   need_img=True, k_off=0, n_img=None):
+    def pair_weights(self, dS, cnt, T, mean_mode):
+        return dS.float() / ((cnt + 1e-8) if mean_mode == MASKED else float(T))
+
+    def maxsim_bwd(self, txt_op, img_op, argmax, w, T, P, prec, need_txt=True, need_img=True, k_off=0, n_img=None,
+                   generic=False):
         Bt, _, D = txt_op.shape
         n_img = img_op.shape[0] - k_off if n_img is None else n_img
-        g = 1.0 if gscale is None else float(gscale)
         sl = slice(k_off, k_off + n_img)
-        w = dS[:, sl] * g / ((cnt[:, sl] + 1e-8) if mean_mode == MASKED else float(T))     # [Bt,n]
+        w = w[:, sl]                                                                      # [Bt,n]
         arg = argmax[:, sl]                                                               # [Bt,n,T]
         img = img_op[sl]
         dtxt = dimg = None
@@ -63,14 +65,17 @@ class TorchRefKernels:
         diag = Z[idx, row0 + idx]
         return row_lse, col_max, col_sum, diag
 
-    def infonce_grad(self, X, scale, coef, row0, row_lse, col_lse):
+    def infonce_grad(self, X, scale, coef, row0, row_lse, col_lse, cnt=None, out=None):
         B_loc, B = X.shape
         Z = X * scale
         t = torch.exp(Z - row_lse[:, None]) + torch.exp(Z - col_lse[None, :])
         idx = torch.arange(B_loc)
         t[idx, row0 + idx] -= 2.0
         t = t * (coef / (2.0 * B))
-        return t * scale, (t * X).sum().reshape(1)
+        dX = t * scale
+        if cnt is not None:
+            dX = dX / (cnt + 1e-8)
+        return dX, (t * X).sum().reshape(1)
 
     def rank_of_target(self, scores, target):
         scores = scores.float()

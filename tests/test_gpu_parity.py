@@ -74,7 +74,7 @@ def test_maxsim_forward_bf16(K, shape, mode):
     torch.cuda.synchronize()
     ref = O.maxsim_scores_blockwise(ti, tt, mode, block=16)
     torch.testing.assert_close(S.cpu(), ref, rtol=1e-4, atol=2e-6)
-    _check_argmax(arg.cpu().long() & 0xFFFF, ti, tt, f"bf16 {shape}")
+    _check_argmax(K.argmax_as_text_major(arg, Bt, T).cpu(), ti, tt, f"bf16 {shape}")
     if mode == O.MASKED:
         mx, _ = O.maxsim_rowmax(ti, tt)
         assert torch.equal(cnt.cpu(), (mx != 0).float().sum(dim=2))
@@ -90,7 +90,7 @@ def test_maxsim_forward_schedules(K, stream_a, grid):
                                      O.MASKED, True, force_stream_a=stream_a, force_grid=grid)
     torch.cuda.synchronize()
     torch.testing.assert_close(S.cpu(), O.maxsim_scores_blockwise(ti, tt, O.MASKED, 16), rtol=1e-4, atol=2e-6)
-    _check_argmax(arg.cpu().long(), ti, tt, "schedules")
+    _check_argmax(K.argmax_as_text_major(arg, Bt, T).cpu(), ti, tt, "schedules")
 
 
 F32_SHAPES = [(8, 8, 7, 10, 16), (12, 12, 9, 49, 64), (6, 6, 77, 200, 20), (3, 4, 20, 576, 32), (64, 64, 77, 49, 512)]
@@ -105,7 +105,7 @@ def test_maxsim_forward_fp32(K, shape):
     torch.cuda.synchronize()
     ref = O.maxsim_scores_blockwise(ti, tt, O.MASKED, block=16)
     torch.testing.assert_close(S.cpu(), ref, rtol=1e-5, atol=1e-6)
-    _check_argmax(arg.cpu().long() & 0xFFFF, ti, tt, f"fp32 {shape}")
+    _check_argmax(K.argmax_as_text_major(arg, Bt, T).cpu(), ti, tt, f"fp32 {shape}")
 
 
 @pytest.mark.parametrize("prec", ["bf16", "fp32"])
@@ -131,6 +131,37 @@ def test_maxsim_backward(K, prec, shape, mode):
     for ours, ref, n in ((xt.grad.cpu(), dtxt, "dtxt"), (xi.grad.cpu(), dimg, "dimg")):
         tol = 1e-5 * ref.abs().max().item()
         assert (ours - ref).abs().max().item() <= tol, (n, (ours - ref).abs().max().item(), tol)
+
+
+STREAM_SHAPES = [(70, 9, 77, 196, 256), (10, 37, 20, 576, 128), (40, 6, 33, 49, 128), (3, 3, 8, 300, 128),
+                 (9, 5, 130, 257, 128), (33, 70, 9, 17, 512)]
+
+
+@pytest.mark.parametrize("shape", STREAM_SHAPES, ids=str)
+def test_maxsim_backward_streaming_kernels(K, shape):
+    """TMA-staged streaming K2 (bf16, D % 128 == 0, T >= 8): against the oracle's closed form, against the
+    generic kernels, and as two image shards (k_off / ld_pairs contract of the multi-GPU pipeline)."""
+    Bt, Bi, T, P, D = shape
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=77 + P, pad_text=True, Bt=Bt)
+    ti, tt = _rounded(ti), _rounded(tt)
+    txt_op = K.prepare(tt.cuda(), T, "bf16")
+    img_op = K.prepare(ti.cuda(), K.img_row_stride(P, "bf16"), "bf16")
+    S, cnt, arg = K.maxsim_fwd(txt_op, img_op, T, P, "bf16", O.MASKED, True)
+    dS = torch.randn(Bt, Bi, generator=torch.Generator().manual_seed(5))
+    w = K.pair_weights(dS.cuda(), cnt, T, O.MASKED)
+    dtxt, dimg = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16")
+    gtxt, gimg = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", generic=True)
+    torch.cuda.synchronize()
+    rtxt, rimg = O.maxsim_closed_form_grads(ti, tt, dS, O.MASKED)
+    for ours, gen, ref, n in ((dtxt, gtxt, rtxt, "dtxt"), (dimg[:, :P], gimg[:, :P], rimg, "dimg")):
+        tol = 2e-5 * ref.abs().max().item()
+        assert (ours.cpu() - ref).abs().max().item() <= tol, (n, "stream vs oracle")
+        assert (gen.cpu() - ref).abs().max().item() <= tol, (n, "generic vs oracle")
+    if Bi >= 2:
+        h = Bi // 2
+        _, d0 = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, k_off=0, n_img=h)
+        _, d1 = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, k_off=h, n_img=Bi - h)
+        assert torch.equal(torch.cat([d0, d1]), dimg)
 
 
 def test_all_zero_text_edge_case(K):
@@ -175,6 +206,13 @@ def test_infonce_kernels(K, B_loc, B, row0):
     dX_r, dsc_r = R.infonce_grad(X, scale, coef, row0, rl_r, cl)
     assert (dX.cpu() - dX_r).abs().max() <= 2e-5 * dX_r.abs().max()
     assert abs(dsc.item() - dsc_r.item()) <= 1e-4 * max(abs(dsc_r.item()), 1e-3)
+    # fused pair-weight output (token logits): dX / (cnt + 1e-8), written in place over X
+    cnt = torch.randint(0, 78, (B_loc, B), generator=g).float()
+    Xc = X.cuda().clone()
+    w, _ = K.infonce_grad(Xc, scale.cuda(), coef.cuda(), row0, rl_r.cuda(), cl.cuda(), cnt=cnt.cuda(), out=Xc)
+    w_r = dX_r / (cnt + 1e-8)
+    assert w.data_ptr() == Xc.data_ptr()
+    assert ((w.cpu() - w_r).abs() <= 2e-5 * w_r.abs().max() + 1e-5 * w_r.abs()).all()
 
 
 # ---------------------------------------------------------------------------------------------------
@@ -241,11 +279,15 @@ def test_cfg1_headline(K):
     for g, n in zip(grads, NAMES):
         assert (g - r_grads[n]).abs().max().item() <= 1e-5 * r_grads[n].abs().max().item(), n
     # same shape through the tensor-core path
+    # (gradients are compared with the oracle on the bf16-ROUNDED inputs, i.e. what the reference's einsum
+    # sees under bf16 autocast: rounding the operands legitimately flips near-tied argmaxes, which moves
+    # gradient mass between patches relative to the fp32 run)
     losses_b, grads_b, _ = _run_loss(inputs, 1 / 0.07, 0.5, autocast=True)
+    _, rb_grads = O.loss_and_grads(*[_rounded(t) for t in inputs], 1 / 0.07, 0.5)
     for k in losses_b:
         assert abs(losses_b[k] - float(z[k])) <= 1e-2 * abs(float(z[k])), k
     for g, n in zip(grads_b, NAMES):
-        rel = (g - r_grads[n]).norm() / r_grads[n].norm()
+        rel = (g - rb_grads[n]).norm() / rb_grads[n].norm()
         assert rel <= 1e-2, (n, rel.item())
 
 
