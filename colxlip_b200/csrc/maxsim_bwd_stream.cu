@@ -88,14 +88,24 @@ struct __align__(8) StreamBarriers {
 // ------------------------------------------------------------------------------------------------
 // dTxt
 // ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void sts_v2(uint32_t addr, float a, uint32_t b) {
+  asm volatile("st.shared.v2.b32 [%0], {%1, %2};" ::"r"(addr), "f"(a), "r"(b) : "memory");
+}
+
+// Warp layout: warps 0..NWC-1 consume (R rows each, lanes span the DS-wide slice), warp NWC issues TMA.
+// Each consumer warp prepares the (weight, slab offset) entries of ITS OWN rows (lane <-> row, loads
+// issued two images ahead) and exchanges them through a private double-buffered smem strip, so the only
+// cross-warp synchronisation is the slab ring.
 template <int DS, int R, int NWC>
 __global__ void __launch_bounds__((NWC + 1) * 32, 1)
 maxsim_bwd_dtxt_stream_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdStreamParams p) {
   constexpr int VEC = DS / 32;
   constexpr int ROWS = NWC * R;
+  static_assert(R == 32 || R == 16, "lane <-> row entry production");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
   StreamBarriers* bars = reinterpret_cast<StreamBarriers*>(smem + p.stages * p.stage_bytes);
+  uint8_t* ent_area = reinterpret_cast<uint8_t*>(bars + 1);          // [NWC][2][R] entries
 
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
@@ -104,7 +114,7 @@ maxsim_bwd_dtxt_stream_kernel(const __grid_constant__ CUtensorMap tmImg, const B
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(smem_u32(&bars->full[s]), 33);     // 32 entry-writer lanes + the TMA-issuing arrive
+      mbar_init(smem_u32(&bars->full[s]), 1);
       mbar_init(smem_u32(&bars->empty[s]), NWC);
     }
     fence_barrier_init();
@@ -113,23 +123,45 @@ maxsim_bwd_dtxt_stream_kernel(const __grid_constant__ CUtensorMap tmImg, const B
   __syncthreads();
 
   if (warp == NWC) {
-    // ============ producer warp: TMA slab + per-row (w, slab byte offset) entries ============
-    // lane handles rows i*32 + lane; argmax bytes are prefetched two images ahead (they stream from
-    // DRAM exactly once), weights come through L1 (32 consecutive images share a line).
-    constexpr int PER = ROWS / 32;
-    const float* wrow[PER];
-    uint32_t qpre[2][PER];
-    const size_t esz_base = static_cast<size_t>(p.k_off) * p.ld_arg + r0 + lane;
-#pragma unroll
-    for (int i = 0; i < PER; ++i) {
-      const int r = r0 + i * 32 + lane;
-      wrow[i] = r < p.rows ? p.w + static_cast<size_t>(r / p.T) * p.ld_pairs + p.k_off : nullptr;
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int k = 0; k < p.Bi; ++k) {
+        mbar_wait(smem_u32(&bars->empty[stage]), phase ^ 1);
+        const uint32_t st = smem_u32(smem + stage * p.stage_bytes);
+        const uint32_t full = smem_u32(&bars->full[stage]);
+        mbar_arrive_expect_tx(full, p.tile_bytes);
+        for (int q0 = 0; q0 < p.P; q0 += 256) tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, k * p.p_stride + q0);
+        if (++stage == p.stages) { stage = 0; phase ^= 1; }
+      }
     }
+  } else {
+    float acc[R][VEC];
 #pragma unroll
-    for (int b = 0; b < 2; ++b)
+    for (int j = 0; j < R; ++j)
 #pragma unroll
-      for (int i = 0; i < PER; ++i)
-        qpre[b][i] = (wrow[i] != nullptr && b < p.Bi) ? load_q(p, esz_base + static_cast<size_t>(b) * p.ld_arg + i * 32) : 0;
+      for (int i = 0; i < VEC; ++i) acc[j][i] = 0.f;
+
+    // entry production state (lanes >= R idle when R == 16)
+    const int my_row = min(r0 + warp * R + (lane % R), p.rows - 1);       // clamped: tail rows are never stored
+    const uint8_t* qptr8 = reinterpret_cast<const uint8_t*>(p.argmax) + static_cast<size_t>(p.k_off) * p.ld_arg + my_row;
+    const uint16_t* qptr16 = reinterpret_cast<const uint16_t*>(p.argmax) + static_cast<size_t>(p.k_off) * p.ld_arg + my_row;
+    const float* wptr = p.w + static_cast<size_t>(my_row / p.T) * p.ld_pairs + p.k_off;
+    const bool u16 = p.argmax_u16 != 0;
+    auto ldq = [&](int k) -> uint32_t {
+      const size_t o = static_cast<size_t>(k) * p.ld_arg;
+      return u16 ? static_cast<uint32_t>(__ldg(qptr16 + o)) : static_cast<uint32_t>(__ldg(qptr8 + o));
+    };
+    uint32_t qn[2];
+    float wn[2];
+#pragma unroll
+    for (int b = 0; b < 2; ++b) {
+      const int kk = min(b, p.Bi - 1);
+      qn[b] = ldq(kk);
+      wn[b] = __ldg(wptr + kk);
+    }
+    const uint32_t ent_base = smem_u32(ent_area) + warp * (2 * R * 8);
+    const uint32_t lane_off = lane * VEC * 2;
     int stage = 0;
     uint32_t phase = 0;
     for (int k0 = 0; k0 < p.Bi; k0 += 2) {
@@ -137,56 +169,32 @@ maxsim_bwd_dtxt_stream_kernel(const __grid_constant__ CUtensorMap tmImg, const B
       for (int b = 0; b < 2; ++b) {
         const int k = k0 + b;
         if (k < p.Bi) {
-          mbar_wait(smem_u32(&bars->empty[stage]), phase ^ 1);
-          uint8_t* st = smem + stage * p.stage_bytes;
-          const uint32_t full = smem_u32(&bars->full[stage]);
-          if (lane == 0) {
-            mbar_arrive_expect_tx(full, p.tile_bytes);
-            for (int q0 = 0; q0 < p.P; q0 += 256)
-              tma_load_2d(smem_u32(st + static_cast<size_t>(q0) * DS * 2), &tmImg, full, d0, k * p.p_stride + q0);
+          const uint32_t ebuf = ent_base + b * (R * 8);
+          if (R == 32 || lane < R) sts_v2(ebuf + (lane % R) * 8, wn[b], qn[b] * (DS * 2));
+          __syncwarp();
+          {   // prefetch the entry of image k + 2 (clamped; an unused extra load at the very end is harmless)
+            const int kk = min(k + 2, p.Bi - 1);
+            qn[b] = ldq(kk);
+            wn[b] = __ldg(wptr + kk);
           }
-          Entry* ent = reinterpret_cast<Entry*>(st + p.tile_bytes);
+          mbar_wait(smem_u32(&bars->full[stage]), phase);
+          const uint32_t stl = smem_u32(smem + stage * p.stage_bytes) + lane_off;
 #pragma unroll
-          for (int i = 0; i < PER; ++i) {
-            Entry e;
-            e.q = qpre[b][i] * (DS * 2);
-            e.w = wrow[i] != nullptr ? __ldg(wrow[i] + k) : 0.f;
-            ent[i * 32 + lane] = e;
-            if (k + 2 < p.Bi && wrow[i] != nullptr)
-              qpre[b][i] = load_q(p, esz_base + static_cast<size_t>(k + 2) * p.ld_arg + i * 32);
+          for (int j = 0; j < R; j += 2) {
+            float w0, w1;
+            uint32_t o0, o1;
+            asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=f"(w0), "=r"(o0), "=f"(w1), "=r"(o1) : "r"(ebuf + j * 8));
+            uint32_t v0[VEC / 2], v1[VEC / 2];
+            PackedLoad<VEC>::ld(stl + o0, v0);
+            PackedLoad<VEC>::ld(stl + o1, v1);
+            fma_row<VEC>(acc[j], v0, w0);
+            fma_row<VEC>(acc[j + 1], v1, w1);
           }
-          mbar_arrive(full);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bars->empty[stage]));
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
-    }
-  } else {
-    // ============ consumer warps: R rows each, lanes span the D-slice ============
-    float acc[R][VEC];
-#pragma unroll
-    for (int j = 0; j < R; ++j)
-#pragma unroll
-      for (int i = 0; i < VEC; ++i) acc[j][i] = 0.f;
-    int stage = 0;
-    uint32_t phase = 0;
-    const uint32_t lane_off = lane * VEC * 2;
-    for (int k = 0; k < p.Bi; ++k) {
-      mbar_wait(smem_u32(&bars->full[stage]), phase);
-      const uint32_t st = smem_u32(smem + stage * p.stage_bytes);
-      const uint32_t ent = st + p.tile_bytes + warp * R * 8;
-      const uint32_t stl = st + lane_off;
-#pragma unroll
-      for (int j = 0; j < R; ++j) {
-        float w;
-        uint32_t qo;
-        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(w), "=r"(qo) : "r"(ent + j * 8));
-        uint32_t v[VEC / 2];
-        PackedLoad<VEC>::ld(stl + qo, v);
-        fma_row<VEC>(acc[j], v, w);
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(smem_u32(&bars->empty[stage]));
-      if (++stage == p.stages) { stage = 0; phase ^= 1; }
     }
 #pragma unroll
     for (int j = 0; j < R; ++j) {
@@ -224,10 +232,16 @@ __device__ __forceinline__ void fma_select(float (&acc)[G][VEC], const uint32_t 
   }
 }
 
+// Warp layout: warps 0..nwc-1 consume (warp g owns patches [g*G, g*G+G)), warps nwc..nwc+RT/32-1 produce:
+// producer warp pw prepares the (weight, patch) entry of row pw*32 + lane of every tile (argmax bytes are
+// prefetched two tiles ahead; the weights of 32 consecutive texts sit in one register per lane, fetched a
+// whole batch ahead) and producer warp 0 also issues the TMA load of the text-row tile.
+// The host guarantees T >= 8: a tile's RT = 128 rows span at most 17 texts, i.e. at most two batches.
 template <int DS, int G, int RT, int MAXW>
 __global__ void __launch_bounds__(MAXW * 32, 1)
 maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdStreamParams p, int nwc) {
   constexpr int VEC = DS / 32;
+  constexpr int NPW = RT / 32;
   static_assert(G <= 24, "patch group too large");
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
@@ -241,7 +255,7 @@ maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const B
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < p.stages; ++s) {
-      mbar_init(smem_u32(&bars->full[s]), 33);
+      mbar_init(smem_u32(&bars->full[s]), NPW + 1);     // one arrive per producer warp + the expect_tx arrive
       mbar_init(smem_u32(&bars->empty[s]), nwc);
     }
     fence_barrier_init();
@@ -249,31 +263,24 @@ maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const B
   }
   __syncthreads();
 
-  if (warp == nwc) {
-    // ============ producer warp: TMA text-row tile + per-row (w, patch id) entries ============
-    // Weights of 32 consecutive texts live in one register per lane (w_cur / w_nxt, strided loads with
-    // a whole batch of lead time); argmax bytes are prefetched two tiles ahead.  The host guarantees
-    // T >= 8, so the RT rows of a tile span at most RT/8 + 1 <= 32 texts (never more than two batches).
-    constexpr int PER = RT / 32;
-    const size_t abase = static_cast<size_t>(p.k_off + k) * p.ld_arg + lane;
+  if (warp >= nwc) {
+    const int pw = warp - nwc;
+    const int slot = pw * 32 + lane;                     // row of the tile this lane prepares
+    const bool u16 = p.argmax_u16 != 0;
+    const uint8_t* q8 = reinterpret_cast<const uint8_t*>(p.argmax) + static_cast<size_t>(p.k_off + k) * p.ld_arg;
+    const uint16_t* q16 = reinterpret_cast<const uint16_t*>(p.argmax) + static_cast<size_t>(p.k_off + k) * p.ld_arg;
+    auto ldq = [&](int r) -> uint32_t {
+      if (r >= p.rows) return 0xFFFFu;                   // owned by nobody
+      return u16 ? static_cast<uint32_t>(__ldg(q16 + r)) : static_cast<uint32_t>(__ldg(q8 + r));
+    };
     const float* wcol = p.w + p.k_off + k;
     auto load_w = [&](int m) { return m < p.Bt ? __ldg(wcol + static_cast<size_t>(m) * p.ld_pairs) : 0.f; };
     int m_base = 0;
     float w_cur = load_w(lane), w_nxt = load_w(32 + lane);
-    int m_slot[PER], n_slot[PER];          // (text, token) of this lane's rows in the current tile
-#pragma unroll
-    for (int i = 0; i < PER; ++i) {
-      m_slot[i] = (i * 32 + lane) / p.T;
-      n_slot[i] = (i * 32 + lane) - m_slot[i] * p.T;
-    }
-    uint32_t qpre[2][PER];
-#pragma unroll
-    for (int b = 0; b < 2; ++b)
-#pragma unroll
-      for (int i = 0; i < PER; ++i) {
-        const int r = b * RT + i * 32 + lane;
-        qpre[b][i] = r < p.rows ? load_q(p, abase + b * RT + i * 32) : 0xFFFFu;
-      }
+    int m_row = slot / p.T;                              // text of this lane's row in the current tile
+    int n_row = slot - m_row * p.T;
+    int m_first = 0, n_first = 0;                        // text / token of the tile's first row (warp-uniform)
+    uint32_t qn[2] = {ldq(slot), ldq(RT + slot)};
     int stage = 0;
     uint32_t phase = 0;
     for (int t0 = 0; t0 < num_tiles; t0 += 2) {
@@ -281,42 +288,35 @@ maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const B
       for (int b = 0; b < 2; ++b) {
         const int t = t0 + b;
         if (t < num_tiles) {
-          // advance the weight batches so that the first text of this tile is inside w_cur
-          const int m_first = (t * RT) / p.T;
-          while (m_first >= m_base + 32) {
+          while (m_first >= m_base + 32) {               // keep the tile's first text inside w_cur
             m_base += 32;
             w_cur = w_nxt;
             w_nxt = load_w(m_base + 32 + lane);
           }
+          const int mi = min(m_row, p.Bt - 1) - m_base;  // 0 .. 63
+          const float wa = __shfl_sync(0xffffffffu, w_cur, mi & 31);
+          const float wb = __shfl_sync(0xffffffffu, w_nxt, mi & 31);
+          const float wv = mi < 32 ? wa : wb;
           mbar_wait(smem_u32(&bars->empty[stage]), phase ^ 1);
-          uint8_t* st = smem + stage * p.stage_bytes;
+          const uint32_t st = smem_u32(smem + stage * p.stage_bytes);
           const uint32_t full = smem_u32(&bars->full[stage]);
-          if (lane == 0) {
+          if (pw == 0 && lane == 0) {
             mbar_arrive_expect_tx(full, p.tile_bytes);
-            tma_load_2d(smem_u32(st), &tmTxt, full, d0, t * RT);     // rows past the end are zero-filled
+            tma_load_2d(st, &tmTxt, full, d0, t * RT);   // rows past the end are zero-filled
           }
-          Entry* ent = reinterpret_cast<Entry*>(st + p.tile_bytes);
-#pragma unroll
-          for (int i = 0; i < PER; ++i) {
-            const int r = t * RT + i * 32 + lane;
-            const int mi = min(m_slot[i], p.Bt - 1) - m_base;         // 0 .. 63
-            n_slot[i] += RT;
-            while (n_slot[i] >= p.T) { n_slot[i] -= p.T; ++m_slot[i]; }
-            const float wa = __shfl_sync(0xffffffffu, w_cur, mi & 31);
-            const float wb = __shfl_sync(0xffffffffu, w_nxt, mi & 31);
-            Entry e;
-            e.w = mi < 32 ? wa : wb;
-            e.q = r < p.rows ? qpre[b][i] : 0xFFFFu;                  // 0xFFFF: owned by nobody
-            ent[i * 32 + lane] = e;
-            const int r2 = r + 2 * RT;
-            qpre[b][i] = r2 < p.rows ? load_q(p, abase + static_cast<size_t>(t + 2) * RT + i * 32) : 0xFFFFu;
-          }
-          mbar_arrive(full);
+          sts_v2(st + p.tile_bytes + slot * 8, wv, qn[b]);
+          __syncwarp();
+          if (lane == 0) mbar_arrive(full);
+          qn[b] = ldq((t + 2) * RT + slot);
+          n_row += RT;
+          while (n_row >= p.T) { n_row -= p.T; ++m_row; }
+          n_first += RT;
+          while (n_first >= p.T) { n_first -= p.T; ++m_first; }
           if (++stage == p.stages) { stage = 0; phase ^= 1; }
         }
       }
     }
-  } else if (warp < nwc) {
+  } else {
     // ============ consumer warp `warp` owns patches [warp*G, warp*G + G) ============
     float acc[G][VEC];
 #pragma unroll
@@ -330,12 +330,13 @@ maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const B
     for (int t = 0; t < num_tiles; ++t) {
       mbar_wait(smem_u32(&bars->full[stage]), phase);
       const uint32_t st = smem_u32(smem + stage * p.stage_bytes);
-      const uint32_t ent = st + p.tile_bytes;
-#pragma unroll 1
+      const uint32_t ent = st + p.tile_bytes + lane * 8;
+      const uint32_t stl = st + lane_off;
+#pragma unroll
       for (int c = 0; c < RT / 32; ++c) {
         float w;
         uint32_t q;
-        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(w), "=r"(q) : "r"(ent + (c * 32 + lane) * 8));
+        asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=f"(w), "=r"(q) : "r"(ent + c * 256));
         const uint32_t ql = q - q_lo;
         uint32_t mask = __ballot_sync(0xffffffffu, ql < static_cast<uint32_t>(G));
         while (mask) {
@@ -344,7 +345,7 @@ maxsim_bwd_dimg_stream_kernel(const __grid_constant__ CUtensorMap tmTxt, const B
           const float wj = __shfl_sync(0xffffffffu, w, j);
           const int qj = __shfl_sync(0xffffffffu, static_cast<int>(ql), j);
           uint32_t v[VEC / 2];
-          PackedLoad<VEC>::ld(st + (c * 32 + j) * (DS * 2) + lane_off, v);
+          PackedLoad<VEC>::ld(stl + (c * 32 + j) * (DS * 2), v);
           fma_select<VEC, G>(acc, v, wj, qj);
         }
       }
@@ -418,8 +419,8 @@ static int launch_dtxt(const void* img, BwdStreamParams p, int max_smem, cudaStr
   const int box_rows = p.P < 256 ? p.P : 256;
   const int slab_rows = round_up_i(p.P, box_rows);
   p.tile_bytes = slab_rows * DS * 2;
-  p.stage_bytes = round_up_i(p.tile_bytes + ROWS * 8, 128);
-  const int overhead = 128 + static_cast<int>(sizeof(StreamBarriers));
+  p.stage_bytes = round_up_i(p.tile_bytes, 128);
+  const int overhead = 128 + static_cast<int>(sizeof(StreamBarriers)) + NWC * 2 * R * 8;
   int stages = (max_smem - overhead) / p.stage_bytes;
   if (stages < 2) return CXL_ERR_UNSUPPORTED;
   p.stages = stages > 4 ? 4 : stages;
@@ -438,7 +439,7 @@ static int launch_dtxt(const void* img, BwdStreamParams p, int max_smem, cudaStr
 template <int DS, int G, int RT, int MAXW>
 static int launch_dimg(const void* txt, BwdStreamParams p, int max_smem, cudaStream_t stream) {
   const int nwc = (p.P + G - 1) / G;
-  if (nwc + 1 > MAXW) return CXL_ERR_UNSUPPORTED;
+  if (nwc + RT / 32 > MAXW) return CXL_ERR_UNSUPPORTED;
   p.tile_bytes = RT * DS * 2;
   p.stage_bytes = round_up_i(p.tile_bytes + RT * 8, 128);
   const int overhead = 128 + static_cast<int>(sizeof(StreamBarriers));
@@ -452,7 +453,7 @@ static int launch_dimg(const void* txt, BwdStreamParams p, int max_smem, cudaStr
   auto kern = maxsim_bwd_dimg_stream_kernel<DS, G, RT, MAXW>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid(p.Bi, p.D / DS);
-  kern<<<grid, (nwc + 1) * 32, smem_bytes, stream>>>(tm, p, nwc);
+  kern<<<grid, (nwc + RT / 32) * 32, smem_bytes, stream>>>(tm, p, nwc);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }
@@ -482,8 +483,8 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     if (rc != CXL_OK) return rc;
   }
   if (dimg != nullptr) {
-    if (P <= 31 * 8) rc = launch_dimg<128, 8, 128, 32>(txt, p, max_smem, stream);
-    else if (P <= 25 * 24) rc = launch_dimg<64, 24, 128, 26>(txt, p, max_smem, stream);
+    if (P <= 28 * 8) rc = launch_dimg<128, 8, 128, 32>(txt, p, max_smem, stream);
+    else if (P <= 24 * 24) rc = launch_dimg<64, 24, 128, 28>(txt, p, max_smem, stream);
     else rc = CXL_ERR_UNSUPPORTED;
     if (rc != CXL_OK) return rc;
   }
