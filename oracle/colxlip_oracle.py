@@ -155,19 +155,29 @@ def loss_and_grads(image_features, text_features, token_image_features, token_te
              "logit_scale": ls.grad})
 
 
-def maxsim_closed_form_grads(img_tok, txt_tok, dS, mode: int = MASKED):
+def maxsim_closed_form_grads(img_tok, txt_tok, dS, mode: int = MASKED, round_w_bf16: bool = False,
+                             arg_override: Optional[torch.Tensor] = None):
     """Closed-form backward of maxsim_scores: no autograd, numpy-style loops.
+
+    round_w_bf16: round the pair weight w to bf16 first -- what the reference's own backward bmm sees
+    under bf16 autocast (dS arrives in bf16), and what the fast CUDA backward kernels compute with.
 
     cnt = nnz + 1e-8 (or T), w = dS / cnt,
     dTxt[m,n] = sum_k w[m,k] img[k,q*],  dImg[k,q] = sum_{m,n:q*=q} w[m,k] txt[m,n].
     """
     mx, arg = maxsim_rowmax(img_tok.float(), txt_tok.float())
+    if arg_override is not None:
+        # backward-only checks: scatter through a given argmax [Bt,Bi,T] (near-tied maxima may legitimately
+        # resolve differently between accumulate orders; argmax parity itself is tested on the forward)
+        arg = arg_override
     Bt, Bi, T = mx.shape
     if mode == MEAN:
         cnt = torch.full((Bt, Bi), float(T), device=img_tok.device)
     else:
         cnt = (mx != 0).float().sum(dim=2) + 1e-8
     w = dS / cnt
+    if round_w_bf16:
+        w = w.to(torch.bfloat16).float()
     dtxt = torch.zeros_like(txt_tok, dtype=torch.float32)
     dimg = torch.zeros_like(img_tok, dtype=torch.float32)
     for m in range(Bt):

@@ -127,14 +127,16 @@ def test_maxsim_backward(K, prec, shape, mode):
         S.backward(dS.cuda())
     finally:
         L.set_precision("auto")
-    dtxt, dimg = O.maxsim_closed_form_grads(ti, tt, dS, mode)
+    # bf16 shapes with D % 128 == 0 run the fast kernels, which round the pair weight to bf16 (FHFMA.BF16)
+    fast = prec == "bf16" and D % 128 == 0
+    dtxt, dimg = O.maxsim_closed_form_grads(ti, tt, dS, mode, round_w_bf16=fast)
     for ours, ref, n in ((xt.grad.cpu(), dtxt, "dtxt"), (xi.grad.cpu(), dimg, "dimg")):
         tol = 1e-5 * ref.abs().max().item()
         assert (ours - ref).abs().max().item() <= tol, (n, (ours - ref).abs().max().item(), tol)
 
 
 STREAM_SHAPES = [(70, 9, 77, 196, 256), (10, 37, 20, 576, 128), (40, 6, 33, 49, 128), (3, 3, 8, 300, 128),
-                 (9, 5, 130, 257, 128), (33, 70, 9, 17, 512)]
+                 (9, 5, 130, 257, 128), (33, 70, 9, 17, 512), (5, 6, 3, 20, 128), (300, 11, 77, 196, 512)]
 
 
 @pytest.mark.parametrize("shape", STREAM_SHAPES, ids=str)
@@ -152,10 +154,15 @@ def test_maxsim_backward_streaming_kernels(K, shape):
     dtxt, dimg = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16")
     gtxt, gimg = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", generic=True)
     torch.cuda.synchronize()
-    rtxt, rimg = O.maxsim_closed_form_grads(ti, tt, dS, O.MASKED)
-    for ours, gen, ref, n in ((dtxt, gtxt, rtxt, "dtxt"), (dimg[:, :P], gimg[:, :P], rimg, "dimg")):
+    a = K.argmax_as_text_major(arg, Bt, T).cpu()
+    rtxt, rimg = O.maxsim_closed_form_grads(ti, tt, dS, O.MASKED, arg_override=a)
+    # the fast kernels multiply with the bf16-rounded pair weight (the reference's own bmm precision under
+    # autocast): tight against the oracle with the same rounding, within the bf16 tolerance against fp32 w
+    btxt, bimg = O.maxsim_closed_form_grads(ti, tt, dS, O.MASKED, round_w_bf16=True, arg_override=a)
+    for ours, gen, ref, refb, n in ((dtxt, gtxt, rtxt, btxt, "dtxt"), (dimg[:, :P], gimg[:, :P], rimg, bimg, "dimg")):
         tol = 2e-5 * ref.abs().max().item()
-        assert (ours.cpu() - ref).abs().max().item() <= tol, (n, "stream vs oracle")
+        assert (ours.cpu() - refb).abs().max().item() <= tol, (n, "fast vs oracle(bf16 w)")
+        assert (ours.cpu() - ref).abs().max().item() <= 1e-2 * ref.abs().max().item(), (n, "fast vs oracle")
         assert (gen.cpu() - ref).abs().max().item() <= tol, (n, "generic vs oracle")
     if Bi >= 2:
         h = Bi // 2
@@ -264,7 +271,9 @@ def test_loss_bf16_autocast_vs_reference_golden(path):
         assert abs(losses[k] - float(z[k])) <= 1e-2 * max(1.0, abs(float(z[k]))), k
     for g, n in zip(grads, NAMES):
         ref = r_grads[n]
-        assert (g - ref).abs().max().item() <= 5e-5 * ref.abs().max().item() + 1e-9, n
+        # token grads: the fast backward rounds the pair weights to bf16 (rel 2^-9 per term) when D % 128 == 0
+        tol = 1e-2 if (n.startswith("token") and ref.shape[-1] % 128 == 0) else 5e-5
+        assert (g - ref).abs().max().item() <= tol * ref.abs().max().item() + 1e-9, n
     assert abs(gls - r_grads["logit_scale"].item()) <= 1e-4 * max(1e-3, abs(r_grads["logit_scale"].item()))
 
 
