@@ -297,6 +297,199 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   }
 }
 
+// ------------------------------------------------------------------------------------------------
+// K1, CTA-pair variant (cta_group::2): one UMMA covers 256 text-token rows x one image.  Each CTA of the pair
+// keeps ITS 128-row text tile resident and streams only HALF of every image tile (n_tile/2 patch rows), so the
+// per-SM L2->smem traffic and the shared-memory operand reads of the B operand are halved against the single-
+// CTA kernel, which is bound by the 128 B/clk shared-memory port (TMA writes + UMMA operand reads).
+// Barriers: the even CTA owns a_full / b_full (both CTAs' TMA loads credit them) and tmem_empty (8 epilogue
+// warps); b_empty / a_empty / tmem_full exist in both CTAs and are signalled by multicast tcgen05.commit.
+// Used for 128 < P <= 256 (one image per N tile); other geometries run the single-CTA kernel above.
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                      const FwdTcParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* smem_a = smem;
+  uint8_t* smem_ring = smem + p.num_kb * kABlockBytes;
+  FwdTcBarriers* bars = reinterpret_cast<FwdTcBarriers*>(smem_ring + p.num_stages * p.stage_bytes);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t rank = cluster_ctarank();              // 0 = even CTA (issues the MMAs)
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+  const int half_rows = p.n_tile >> 1;                  // image-tile rows loaded by each CTA
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < p.num_stages; ++s) {
+      mbar_init(smem_u32(&bars->b_full[s]), 1);
+      mbar_init(smem_u32(&bars->b_empty[s]), 1);
+    }
+    mbar_init(smem_u32(&bars->a_full), 1);
+    mbar_init(smem_u32(&bars->a_empty), 1);
+    for (int b = 0; b < 2; ++b) {
+      mbar_init(smem_u32(&bars->tmem_full[b]), 1);
+      mbar_init(smem_u32(&bars->tmem_empty[b]), 8);    // 4 epilogue warps of each CTA (even CTA's copy is used)
+    }
+    fence_barrier_init();
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 2) tmem_alloc_512_2cta(smem_u32(&bars->tmem_base));
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                    // peer barriers initialised, peer TMEM allocated
+  tc_fence_after();
+  const uint32_t tmem_base = bars->tmem_base;
+
+  if (warp == 0 && lane == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t a_phase = 0;
+    const uint32_t a_full = smem_u32(&bars->a_full);
+    for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
+      const int chunk = unit / p.num_m_tiles;            // num_m_tiles counts 256-row PAIRS here
+      const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      mbar_wait(smem_u32(&bars->a_empty), a_phase ^ 1);        // previous unit's MMAs are done with A
+      if (rank == 0) mbar_arrive_expect_tx(a_full, 2 * p.num_kb * kABlockBytes);
+      for (int kb = 0; kb < p.num_kb; ++kb)
+        tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
+      a_phase ^= 1;
+      for (int j = j0; j < j1; ++j) {
+        const int row0 = j * p.p_stride + static_cast<int>(rank) * half_rows;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(smem_u32(&bars->b_empty[stage]), phase ^ 1);
+          const uint32_t full = smem_u32(&bars->b_full[stage]);
+          if (rank == 0) mbar_arrive_expect_tx(full, 2 * p.b_block_bytes);
+          tma_load_2d_2cta(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0);
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1 && lane == 0 && rank == 0) {
+    // ===================== MMA issuer (even CTA only) =====================
+    const uint32_t idesc = umma_idesc_bf16(2 * kBlockM, p.n_tile);
+    int stage = 0;
+    uint32_t phase = 0;
+    uint32_t a_phase = 0;
+    int buf = 0;
+    uint32_t acc_phase = 0;
+    for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
+      const int chunk = unit / p.num_m_tiles;
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      mbar_wait(smem_u32(&bars->a_full), a_phase);
+      a_phase ^= 1;
+      for (int j = j0; j < j1; ++j) {
+        mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // both CTAs' epilogues drained this buffer
+        tc_fence_after();
+        const uint32_t tmem_d = tmem_base + buf * 256;
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          mbar_wait(smem_u32(&bars->b_full[stage]), phase);
+          tc_fence_after();
+          const uint32_t a_addr = smem_u32(smem_a + kb * kABlockBytes);
+          const uint32_t b_addr = smem_u32(smem_ring + stage * p.stage_bytes);
+#pragma unroll
+          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
+            const uint64_t da = umma_smem_desc_sw128(a_addr + k * kUmmaK * 2);
+            const uint64_t db = umma_smem_desc_sw128(b_addr + k * kUmmaK * 2);
+            umma_bf16_2cta(tmem_d, da, db, idesc, (kb | k) != 0);
+          }
+          umma_commit_2cta(smem_u32(&bars->b_empty[stage]), 3);        // frees the ring slot in both CTAs
+          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2cta(smem_u32(&bars->tmem_full[buf]), 3);          // accumulator ready in both CTAs
+        buf ^= 1;
+        if (buf == 0) acc_phase ^= 1;
+      }
+      umma_commit_2cta(smem_u32(&bars->a_empty), 3);
+    }
+  } else if (warp >= 4) {
+    // ===================== epilogue (both CTAs): max/argmax over patches, per-text sums =====================
+    const int quad = warp & 3;
+    const int row_in_tile = quad * 32 + lane;
+    int buf = 0;
+    uint32_t acc_phase = 0;
+    const int nchunks = (p.P + 15) >> 4;
+    for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
+      const int chunk = unit / p.num_m_tiles;
+      const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
+      const int j0 = chunk * p.tiles_per_unit;
+      const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
+      const int R = m_tile * kBlockM + row_in_tile;
+      const bool valid = R < p.rows_a;
+      const int m = R / p.T;
+      uint32_t same = 0;                                  // segmented-reduction predicates: lanes of one text are contiguous
+#pragma unroll
+      for (int o = 0; o < 5; ++o) {
+        const int off = 1 << o;
+        const int mo = __shfl_down_sync(0xffffffffu, m, off);
+        if (lane + off < 32 && mo == m) same |= 1u << o;
+      }
+      const int m_prev = __shfl_up_sync(0xffffffffu, m, 1);
+      const bool head = valid && (lane == 0 || m_prev != m);
+      float* s_row = p.S + static_cast<size_t>(m) * p.Bi;
+      float* c_row = p.cnt != nullptr ? p.cnt + static_cast<size_t>(m) * p.Bi : nullptr;
+
+      for (int k = j0; k < j1; ++k) {                     // one image per tile
+        mbar_wait(smem_u32(&bars->tmem_full[buf]), acc_phase);
+        tc_fence_after();
+        const uint32_t cbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + buf * 256;
+        float best = -INFINITY;
+        int bidx = 0;
+        uint32_t va[16], vb[16];
+        tmem_ld16(cbase, va);
+        for (int c = 0; c < nchunks; c += 2) {
+          tmem_wait_ld16(va);
+          if (c + 1 < nchunks) tmem_ld16(cbase + (c + 1) * 16, vb);
+          scan16(va, c * 16, p.P, 0, best, bidx);
+          if (c + 1 < nchunks) {
+            tmem_wait_ld16(vb);
+            if (c + 2 < nchunks) tmem_ld16(cbase + (c + 2) * 16, va);
+            scan16(vb, (c + 1) * 16, p.P, 0, best, bidx);
+          }
+        }
+        // all tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back early
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));
+        buf ^= 1;
+        if (buf == 0) acc_phase ^= 1;
+
+        if (valid && p.argmax != nullptr) {
+          const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
+          if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
+          else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
+        }
+        float v = valid ? best : 0.f;
+        float nz = (valid && best != 0.f) ? 1.f : 0.f;
+#pragma unroll
+        for (int o = 0; o < 5; ++o) {
+          const float tv = __shfl_down_sync(0xffffffffu, v, 1 << o);
+          const float tn = __shfl_down_sync(0xffffffffu, nz, 1 << o);
+          if (same & (1u << o)) { v += tv; nz += tn; }
+        }
+        if (head) {
+          atomicAdd(s_row + k, v);
+          if (c_row != nullptr) atomicAdd(c_row + k, nz);
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                    // no CTA leaves while its peer may still signal it
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc_512_2cta(tmem_base);
+  }
+}
+
 // S <- final score: masked mean  sum / (cnt + 1e-8)   (loss.py:40-44)  or plain mean sum / T (model.py:628)
 __global__ void maxsim_finalize_kernel(float* __restrict__ S, const float* __restrict__ cnt, size_t n, float inv_T,
                                        int mean_mode) {
@@ -394,6 +587,51 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   CXL_CUDA_CHECK(cudaGetDevice(&dev));
   CXL_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
   const int overhead = 1024 /*alignment*/ + static_cast<int>(sizeof(FwdTcBarriers)) + 64;
+
+  // ---- CTA-pair kernel: one image per N tile, both operands' tiles fit, no scheduling overrides ----
+  static const int pair_env = getenv("CXL_K1_PAIR") ? atoi(getenv("CXL_K1_PAIR")) : 1;
+  if (pair_env && p.ipt == 1 && p.parts == 1 && dbg == nullptr && !force_stream_a && force_grid <= 0 &&
+      p.n_tile % 16 == 0) {
+    const int half_bytes = (p.n_tile / 2) * kBlockK * 2;
+    const int half_stage = round_up(half_bytes, 1024);
+    int st2 = (max_smem - overhead - p.num_kb * kABlockBytes) / half_stage;
+    if ((p.n_tile / 2) % 8 == 0 && st2 >= 4) {
+      FwdTcParams q = p;
+      q.a_resident = 1;
+      q.b_block_bytes = half_bytes;
+      q.stage_bytes = half_stage;
+      q.num_stages = st2 > kMaxStages ? kMaxStages : st2;
+      q.num_m_tiles = (p.rows_a + 2 * kBlockM - 1) / (2 * kBlockM);      // 256-row pairs
+      const int sms2 = num_sms();
+      const int clusters = sms2 / 2;
+      long long total2 = static_cast<long long>(q.total_n_tiles) * q.num_m_tiles;
+      long long tpu2 = (total2 + clusters * 8LL - 1) / (clusters * 8LL);
+      tpu2 = (tpu2 + q.num_m_tiles - 1) / q.num_m_tiles;
+      if (tpu2 > 512) tpu2 = 512;
+      if (tpu2 < 1) tpu2 = 1;
+      q.tiles_per_unit = static_cast<int>(tpu2);
+      if (q.tiles_per_unit > q.total_n_tiles) q.tiles_per_unit = q.total_n_tiles;
+      const int chunks2 = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
+      q.num_units = chunks2 * q.num_m_tiles;
+      q.mean_mode = mean_mode;
+      q.argmax_u16 = P > 256;
+      q.S = S; q.cnt = cnt; q.argmax = argmax; q.ld_arg = ld_arg; q.dbg = nullptr;
+      CUtensorMap tmA2, tmB2;
+      int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM);
+      if (rc2 != CXL_OK) return rc2;
+      rc2 = make_tmap(&tmB2, img, static_cast<long long>(Bi) * q.p_stride, D, q.n_tile / 2);
+      if (rc2 != CXL_OK) return rc2;
+      const size_t npairs2 = static_cast<size_t>(Bt) * Bi;
+      CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
+      if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs2 * sizeof(float), stream));
+      const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes;
+      CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+      int ncl = q.num_units < clusters ? q.num_units : clusters;
+      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads, smem2, stream>>>(tmA2, tmB2, q);
+      CXL_CUDA_CHECK(cudaGetLastError());
+      return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
+    }
+  }
   const int b_stage = round_up(p.b_block_bytes, 1024);
   // text tile resident if it leaves room for >= 3 ring stages; otherwise stream A with B
   p.a_resident = 1;
