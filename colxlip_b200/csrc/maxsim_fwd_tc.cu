@@ -47,6 +47,7 @@ struct FwdTcParams {
   void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
   long long ld_arg;
   float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
+  int exp_mode;          // experiments (env CXL_K1_EXP): bit0 = skip the epilogue scan (timing only, wrong results)
 };
 
 struct __align__(8) FwdTcBarriers {
@@ -370,9 +371,17 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         }
       }
     }
-  } else if (warp == 1 && lane == 0 && rank == 0) {
+  } else if (warp == 1 && rank == 0) {
     // ===================== MMA issuer (even CTA only) =====================
+    // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in the uniform
+    // datapath; one elected lane issues the tcgen05 instructions.
     const uint32_t idesc = umma_idesc_bf16(2 * kBlockM, p.n_tile);
+    const uint64_t desc_a0 = umma_smem_desc_sw128(smem_u32(smem_a));
+    const uint64_t desc_b0 = umma_smem_desc_sw128(smem_u32(smem_ring));
+    const uint32_t a_step = kABlockBytes >> 4;            // descriptor address units are 16 bytes
+    const uint32_t b_step = static_cast<uint32_t>(p.stage_bytes) >> 4;
+    const int num_kb = p.num_kb;
+    const int num_stages = p.num_stages;
     int stage = 0;
     uint32_t phase = 0;
     uint32_t a_phase = 0;
@@ -388,25 +397,27 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // both CTAs' epilogues drained this buffer
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * 256;
-        for (int kb = 0; kb < p.num_kb; ++kb) {
+        for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_full[stage]), phase);
           tc_fence_after();
-          const uint32_t a_addr = smem_u32(smem_a + kb * kABlockBytes);
-          const uint32_t b_addr = smem_u32(smem_ring + stage * p.stage_bytes);
+          if (elect_one()) {
+            const uint64_t da = desc_a0 + static_cast<uint64_t>(kb * a_step);
+            const uint64_t db = desc_b0 + static_cast<uint64_t>(stage * b_step);
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            const uint64_t da = umma_smem_desc_sw128(a_addr + k * kUmmaK * 2);
-            const uint64_t db = umma_smem_desc_sw128(b_addr + k * kUmmaK * 2);
-            umma_bf16_2cta(tmem_d, da, db, idesc, (kb | k) != 0);
+            for (int k = 0; k < kBlockK / kUmmaK; ++k)
+              umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);   // +32 bytes per UMMA_K
+            umma_commit_2cta(smem_u32(&bars->b_empty[stage]), 3);      // frees the ring slot in both CTAs
           }
-          umma_commit_2cta(smem_u32(&bars->b_empty[stage]), 3);        // frees the ring slot in both CTAs
-          if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
+          __syncwarp();
+          if (++stage == num_stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit_2cta(smem_u32(&bars->tmem_full[buf]), 3);          // accumulator ready in both CTAs
+        if (elect_one()) umma_commit_2cta(smem_u32(&bars->tmem_full[buf]), 3);   // accumulator ready in both CTAs
+        __syncwarp();
         buf ^= 1;
         if (buf == 0) acc_phase ^= 1;
       }
-      umma_commit_2cta(smem_u32(&bars->a_empty), 3);
+      if (elect_one()) umma_commit_2cta(smem_u32(&bars->a_empty), 3);
+      __syncwarp();
     }
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs): max/argmax over patches, per-text sums =====================
@@ -443,7 +454,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         int bidx = 0;
         uint32_t va[16], vb[16];
         tmem_ld16(cbase, va);
-        for (int c = 0; c < nchunks; c += 2) {
+        for (int c = 0; c < ((p.exp_mode & 1) ? 1 : nchunks); c += 2) {
           tmem_wait_ld16(va);
           if (c + 1 < nchunks) tmem_ld16(cbase + (c + 1) * 16, vb);
           scan16(va, c * 16, p.P, 0, best, bidx);
@@ -604,18 +615,21 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       q.num_m_tiles = (p.rows_a + 2 * kBlockM - 1) / (2 * kBlockM);      // 256-row pairs
       const int sms2 = num_sms();
       const int clusters = sms2 / 2;
-      long long total2 = static_cast<long long>(q.total_n_tiles) * q.num_m_tiles;
-      long long tpu2 = (total2 + clusters * 8LL - 1) / (clusters * 8LL);
-      tpu2 = (tpu2 + q.num_m_tiles - 1) / q.num_m_tiles;
-      if (tpu2 > 512) tpu2 = 512;
-      if (tpu2 < 1) tpu2 = 1;
-      q.tiles_per_unit = static_cast<int>(tpu2);
-      if (q.tiles_per_unit > q.total_n_tiles) q.tiles_per_unit = q.total_n_tiles;
-      const int chunks2 = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
+      // units = (256-row pair, chunk of images).  Whole image sweeps per unit keep the text tile resident longest;
+      // split into more chunks only while the static round-robin over clusters would leave > 3 % of them idle.
+      int chunks2 = 1;
+      for (; chunks2 < 64 && chunks2 < q.total_n_tiles; ++chunks2) {
+        const long long u = static_cast<long long>(chunks2) * q.num_m_tiles;
+        const long long waves = (u + clusters - 1) / clusters;
+        if (static_cast<double>(u) >= 0.97 * static_cast<double>(waves * clusters)) break;
+      }
+      q.tiles_per_unit = (q.total_n_tiles + chunks2 - 1) / chunks2;
+      chunks2 = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
       q.num_units = chunks2 * q.num_m_tiles;
       q.mean_mode = mean_mode;
       q.argmax_u16 = P > 256;
       q.S = S; q.cnt = cnt; q.argmax = argmax; q.ld_arg = ld_arg; q.dbg = nullptr;
+      q.exp_mode = getenv("CXL_K1_EXP") ? atoi(getenv("CXL_K1_EXP")) : 0;
       CUtensorMap tmA2, tmB2;
       int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM);
       if (rc2 != CXL_OK) return rc2;
