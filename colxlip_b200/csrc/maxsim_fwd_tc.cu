@@ -20,6 +20,7 @@ static constexpr int kBlockM = 128;
 static constexpr int kBlockK = 64;     // bf16 elements per 128-byte swizzled row
 static constexpr int kUmmaK = 16;
 static constexpr int kThreads = 256;
+static constexpr int kThreads2 = 384;   // pair kernel: 8 epilogue warps (two per TMEM lane quadrant)
 static constexpr int kABlockBytes = kBlockM * kBlockK * 2;   // 16 KB
 static constexpr int kMaxStages = 8;
 
@@ -58,8 +59,11 @@ struct __align__(8) FwdTcBarriers {
   uint64_t tmem_full[2];
   uint64_t tmem_empty[2];
   uint32_t tmem_base;
+  uint64_t xfull[2];     // pair kernel: xchg[buf] written by the upper-column epilogue warps (count 4)
+  float2 xchg[2][128];   // pair kernel: (max, argmax) handed from the upper-column epilogue warp to the lower one
 };
 
+// Running (max, FIRST argmax -- torch.max semantics) over 16 more accumulator columns; pad columns never win.
 __device__ __forceinline__ void scan16(const uint32_t (&v)[16], int c0, int ncols, int qoff, float& best, int& bidx) {
   float lb = -INFINITY;
   int lj = 0;
@@ -152,9 +156,14 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         }
       }
     }
-  } else if (warp == 1 && lane == 0) {
+  } else if (warp == 1) {
     // ===================== MMA issuer =====================
+    // whole warp runs the warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues
     const uint32_t idesc = umma_idesc_bf16(kBlockM, p.n_tile);
+    const uint64_t desc_a0 = umma_smem_desc_sw128(smem_u32(smem_a));
+    const uint64_t desc_r0 = umma_smem_desc_sw128(smem_u32(smem_ring));
+    const uint32_t a_step = kABlockBytes >> 4;            // descriptor address units are 16 bytes
+    const uint32_t s_step = static_cast<uint32_t>(p.stage_bytes) >> 4;
     int stage = 0;
     uint32_t phase = 0;
     uint32_t a_phase = 0;
@@ -175,23 +184,27 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_full[stage]), phase);
           tc_fence_after();
-          uint8_t* st = smem_ring + stage * p.stage_bytes;
-          const uint32_t a_addr = p.a_resident ? smem_u32(smem_a + kb * kABlockBytes) : smem_u32(st);
-          const uint32_t b_addr = p.a_resident ? smem_u32(st) : smem_u32(st + kABlockBytes);
+          if (elect_one()) {
+            const uint64_t ds = desc_r0 + static_cast<uint64_t>(stage * s_step);
+            const uint64_t da = p.a_resident ? desc_a0 + static_cast<uint64_t>(kb * a_step) : ds;
+            const uint64_t db = p.a_resident ? ds : ds + a_step;
 #pragma unroll
-          for (int k = 0; k < kBlockK / kUmmaK; ++k) {
-            const uint64_t da = umma_smem_desc_sw128(a_addr + k * kUmmaK * 2);
-            const uint64_t db = umma_smem_desc_sw128(b_addr + k * kUmmaK * 2);
-            umma_bf16(tmem_d, da, db, idesc, (kb | k) != 0);
+            for (int k = 0; k < kBlockK / kUmmaK; ++k)
+              umma_bf16(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);       // +32 bytes per UMMA_K
+            umma_commit(smem_u32(&bars->b_empty[stage]));              // frees the ring slot when MMAs retire
           }
-          umma_commit(smem_u32(&bars->b_empty[stage]));                // frees the ring slot when MMAs retire
+          __syncwarp();
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
-        umma_commit(smem_u32(&bars->tmem_full[buf]));                  // accumulator ready for the epilogue
+        if (elect_one()) umma_commit(smem_u32(&bars->tmem_full[buf]));  // accumulator ready for the epilogue
+        __syncwarp();
         buf ^= 1;
         if (buf == 0) acc_phase ^= 1;
       }
-      if (p.a_resident) umma_commit(smem_u32(&bars->a_empty));
+      if (p.a_resident) {
+        if (elect_one()) umma_commit(smem_u32(&bars->a_empty));
+        __syncwarp();
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue: max/argmax over patches, per-text sums =====================
@@ -306,7 +319,7 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 // Barriers: the even CTA owns a_full / b_full (both CTAs' TMA loads credit them) and tmem_empty (8 epilogue
 // warps); b_empty / a_empty / tmem_full exist in both CTAs and are signalled by multicast tcgen05.commit.
 // Used for 128 < P <= 256 (one image per N tile); other geometries run the single-CTA kernel above.
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const FwdTcParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -331,7 +344,8 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     mbar_init(smem_u32(&bars->a_empty), 1);
     for (int b = 0; b < 2; ++b) {
       mbar_init(smem_u32(&bars->tmem_full[b]), 1);
-      mbar_init(smem_u32(&bars->tmem_empty[b]), 8);    // 4 epilogue warps of each CTA (even CTA's copy is used)
+      mbar_init(smem_u32(&bars->xfull[b]), 4);
+      mbar_init(smem_u32(&bars->tmem_empty[b]), 16);   // 8 epilogue warps of each CTA (even CTA's copy is used)
     }
     fence_barrier_init();
     tma_prefetch_desc(&tmA);
@@ -421,11 +435,17 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     }
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs): max/argmax over patches, per-text sums =====================
+    // Two warps per TMEM lane quadrant: warp 4+q scans the lower column chunks of rows 32q..32q+31, warp 8+q the
+    // upper ones and hands its (max, argmax) over through shared memory; the lower warp merges and emits.
     const int quad = warp & 3;
+    const bool upper = warp >= 8;
     const int row_in_tile = quad * 32 + lane;
     int buf = 0;
     uint32_t acc_phase = 0;
     const int nchunks = (p.P + 15) >> 4;
+    const int c_split = (nchunks + 1) >> 1;
+    const int c_lo = upper ? c_split : 0;
+    const int c_hi = upper ? nchunks : c_split;
     for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
       const int chunk = unit / p.num_m_tiles;
       const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
@@ -452,42 +472,55 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const uint32_t cbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + buf * 256;
         float best = -INFINITY;
         int bidx = 0;
-        uint32_t va[16], vb[16];
-        tmem_ld16(cbase, va);
-        for (int c = 0; c < ((p.exp_mode & 1) ? 1 : nchunks); c += 2) {
-          tmem_wait_ld16(va);
-          if (c + 1 < nchunks) tmem_ld16(cbase + (c + 1) * 16, vb);
-          scan16(va, c * 16, p.P, 0, best, bidx);
-          if (c + 1 < nchunks) {
-            tmem_wait_ld16(vb);
-            if (c + 2 < nchunks) tmem_ld16(cbase + (c + 2) * 16, va);
-            scan16(vb, (c + 1) * 16, p.P, 0, best, bidx);
+        if (c_lo < c_hi) {
+          uint32_t va[16], vb[16];
+          tmem_ld16(cbase + c_lo * 16, va);
+          for (int c = c_lo; c < ((p.exp_mode & 1) ? c_lo + 1 : c_hi); c += 2) {
+            tmem_wait_ld16(va);
+            if (c + 1 < c_hi) tmem_ld16(cbase + (c + 1) * 16, vb);
+            scan16(va, c * 16, p.P, 0, best, bidx);
+            if (c + 1 < c_hi) {
+              tmem_wait_ld16(vb);
+              if (c + 2 < c_hi) tmem_ld16(cbase + (c + 2) * 16, va);
+              scan16(vb, (c + 1) * 16, p.P, 0, best, bidx);
+            }
           }
         }
-        // all tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back early
         tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));
+        if (upper) {
+          // all tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back, pass the result on
+          bars->xchg[buf][row_in_tile] = make_float2(best, __int_as_float(bidx));
+          __syncwarp();
+          if (lane == 0) {
+            mbar_arrive(smem_u32(&bars->xfull[buf]));
+            mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));
+          }
+        } else {
+          mbar_wait(smem_u32(&bars->xfull[buf]), acc_phase);
+          const float2 o = bars->xchg[buf][row_in_tile];  // upper columns: wins only if strictly greater
+          __syncwarp();
+          if (lane == 0) mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));   // also orders xchg reuse after this read
+          if (o.x > best) { best = o.x; bidx = __float_as_int(o.y); }
+          if (valid && p.argmax != nullptr) {
+            const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
+            if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
+            else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
+          }
+          float v = valid ? best : 0.f;
+          float nz = (valid && best != 0.f) ? 1.f : 0.f;
+#pragma unroll
+          for (int o2 = 0; o2 < 5; ++o2) {
+            const float tv = __shfl_down_sync(0xffffffffu, v, 1 << o2);
+            const float tn = __shfl_down_sync(0xffffffffu, nz, 1 << o2);
+            if (same & (1u << o2)) { v += tv; nz += tn; }
+          }
+          if (head) {
+            atomicAdd(s_row + k, v);
+            if (c_row != nullptr) atomicAdd(c_row + k, nz);
+          }
+        }
         buf ^= 1;
         if (buf == 0) acc_phase ^= 1;
-
-        if (valid && p.argmax != nullptr) {
-          const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
-          if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
-          else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
-        }
-        float v = valid ? best : 0.f;
-        float nz = (valid && best != 0.f) ? 1.f : 0.f;
-#pragma unroll
-        for (int o = 0; o < 5; ++o) {
-          const float tv = __shfl_down_sync(0xffffffffu, v, 1 << o);
-          const float tn = __shfl_down_sync(0xffffffffu, nz, 1 << o);
-          if (same & (1u << o)) { v += tv; nz += tn; }
-        }
-        if (head) {
-          atomicAdd(s_row + k, v);
-          if (c_row != nullptr) atomicAdd(c_row + k, nz);
-        }
       }
     }
   }
@@ -641,7 +674,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes;
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
       int ncl = q.num_units < clusters ? q.num_units : clusters;
-      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads, smem2, stream>>>(tmA2, tmB2, q);
+      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, stream>>>(tmA2, tmB2, q);
       CXL_CUDA_CHECK(cudaGetLastError());
       return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
     }
