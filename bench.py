@@ -265,7 +265,7 @@ def run_gpu(args):
     pk = peaks()
     flops_rank = 2.0 * b * B * T * P * D
     ach = flops_rank / (k1 * 1e-3) / 1e12
-    roofline = {"bound": "tensor", "kernel": "maxsim_fwd_tc_kernel (K1)", "achieved": ach, "peak": pk["bf16_tflops"],
+    roofline = {"bound": "tensor", "kernel": "maxsim_fwd_tc2_kernel (K1, CTA-pair tcgen05)", "achieved": ach, "peak": pk["bf16_tflops"],
                 "unit": "TFLOP/s", "frac": ach / pk["bf16_tflops"], "traffic": None,
                 "frac_of_sustained_peak": ach / pk["bf16_tflops_sustained"], "peak_source": pk["source"],
                 "kernel_ms": k1, "note": "K1 launch incl. its S/cnt memsets and the finalize kernel, timed alone"}
