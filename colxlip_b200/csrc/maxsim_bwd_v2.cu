@@ -439,16 +439,14 @@ maxsim_bwd_dimg_v2_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
       const uint32_t stl = st + lane_off;
       for (int i = 0; i < n; i += 4) {
         const uint4 e4 = lds128(qa + i * 4);
-        uint32_t e[4] = {e4.x, e4.y, e4.z, e4.w};
-        uint32_t v[4][VEC / 2];
-        // all four operand rows are requested before the first dispatch so their latencies overlap
+        const uint32_t e[4] = {e4.x, e4.y, e4.z, e4.w};
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-          if (u > 0 && i + u >= n) e[u] = static_cast<uint32_t>(G);                      // row 0, weight +0, skipped
-          RowLoad<VEC>::ld(stl + ((e[u] & 0xFFE0u) << OFF_SHIFT), v[u]);
+          const uint32_t eu = (u == 0 || i + u < n) ? e[u] : static_cast<uint32_t>(G);   // row 0, weight +0, skipped
+          uint32_t v[VEC / 2];
+          RowLoad<VEC>::ld(stl + ((eu & 0xFFE0u) << OFF_SHIFT), v);
+          PatchFma<G, VEC>::run(acc, v, eu, eu & 31u);
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) PatchFma<G, VEC>::run(acc, v[u], e[u], e[u] & 31u);
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(empty0 + 8 * stage);
