@@ -35,15 +35,20 @@ struct BwdV2Params {
   int stages;
   int stage_bytes;      // bytes of one ring stage
   int tile_bytes;       // bytes TMA delivers into a stage
-  int nwc;              // dImg: consumer warps
+  // dImg (one chunk of images at a time)
+  const uint8_t* lists; // [chunk_n][n_st][block_bytes] row lists of the chunk (maxsim_bwd_dimg_lists_kernel)
+  int n_st;             // 512-row super-tiles
+  int hdr_words, block_bytes;
+  int chunk_k0;         // first image of the chunk (index into dimg)
+  int chunk_n;          // images in the chunk
 };
 
 struct __align__(8) V2Barriers {
   uint64_t full[8];
   uint64_t empty[8];
   uint64_t ready[8];    // cluster leader only: every CTA of the cluster has freed + armed the stage
-  uint64_t qfull[8];    // dImg: the producers have bucketed the stage's items
 };
+
 
 __device__ __forceinline__ uint32_t pack_entry(float w, uint32_t lo16) {
   return (static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(w))) << 16) | lo16;
@@ -127,6 +132,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
         mbar_arrive_expect_tx(full, p.tile_bytes + qbytes);
         for (int q0 = 0; q0 < p.P; q0 += 256) tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, k * p.p_stride + q0);
         bulk_load_1d(st + p.tile_bytes, qsrc, qbytes, full);
+        if (k + 12 < Bi) bulk_prefetch_l2(qsrc + 12 * qstep, qbytes);     // argmax bytes come from DRAM: stay 12 images ahead
         qsrc += qstep;
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
@@ -217,262 +223,256 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
 // ------------------------------------------------------------------------------------------------
 // dImg
 // ------------------------------------------------------------------------------------------------
-// Patch dispatch: one brx.idx into straight-line FHFMA groups (registers cannot be indexed dynamically).
-template <int G, int VEC> struct PatchFma;
+// Gather formulation with STATIC accumulators (registers cannot be indexed dynamically, and a per-item indirect
+// branch costs far more than the item's FMAs): a quarter warp owns NPO patches of NIMG images for one 64-wide D
+// slice and walks the list of text rows whose argmax is that patch.  The lists come from a cheap pre-pass
+// (one warp per (image, 512-row super-tile)): a deterministic counting sort of the super-tile's rows by patch.
+//
+// List block of one (image, super-tile), `block_bytes` long:
+//   u32 hdr[hdr_words]   hdr[q] = first entry | number of entries << 16   (zero for q >= P)
+//   u32 ent[512]         entries grouped by patch, ascending row inside a patch;
+//                        entry = bf16(w) << 16 | row-in-super-tile * 128   (byte offset of the row in the tile)
+constexpr int kStRows = 512;
 
-#define CXL_F4(L, a, b, c, d)                                                                              \
-  "C" #L ": fma.rn.f32.bf16 %" #a ", x0, wh, %" #a "; fma.rn.f32.bf16 %" #b ", x1, wh, %" #b               \
-  "; fma.rn.f32.bf16 %" #c ", x2, wh, %" #c "; fma.rn.f32.bf16 %" #d ", x3, wh, %" #d "; bra.uni DONE;\n\t"
-#define CXL_F2(L, a, b) \
-  "C" #L ": fma.rn.f32.bf16 %" #a ", x0, wh, %" #a "; fma.rn.f32.bf16 %" #b ", x1, wh, %" #b "; bra.uni DONE;\n\t"
-#define CXL_A4(j) "+f"(acc[j][0]), "+f"(acc[j][1]), "+f"(acc[j][2]), "+f"(acc[j][3])
-#define CXL_A2(j) "+f"(acc[j][0]), "+f"(acc[j][1])
-
-template <> struct PatchFma<8, 4> {
-  // v[0..1]: 4 bf16 channels of the text row, e: entry (bf16 weight in the high half), ql: patch within the group
-  __device__ static __forceinline__ void run(float (&acc)[8][4], const uint32_t (&v)[2], uint32_t e, uint32_t ql) {
-    asm volatile(
-        "{\n\t.reg .b16 x0, x1, x2, x3, wl, wh;\n\t"
-        "mov.b32 {x0, x1}, %33;\n\t mov.b32 {x2, x3}, %34;\n\t mov.b32 {wl, wh}, %35;\n\t"
-        "DT: .branchtargets C0, C1, C2, C3, C4, C5, C6, C7, DONE;\n\t"
-        "brx.idx.uni %32, DT;\n\t"
-        CXL_F4(0, 0, 1, 2, 3) CXL_F4(1, 4, 5, 6, 7) CXL_F4(2, 8, 9, 10, 11) CXL_F4(3, 12, 13, 14, 15)
-        CXL_F4(4, 16, 17, 18, 19) CXL_F4(5, 20, 21, 22, 23) CXL_F4(6, 24, 25, 26, 27) CXL_F4(7, 28, 29, 30, 31)
-        "DONE:\n\t}"
-        : CXL_A4(0), CXL_A4(1), CXL_A4(2), CXL_A4(3), CXL_A4(4), CXL_A4(5), CXL_A4(6), CXL_A4(7)
-        : "r"(ql), "r"(v[0]), "r"(v[1]), "r"(e));
-  }
+struct DimgListParams {
+  const void* argmax;   // [k_off + Bi][ld_arg] image-major
+  long long ld_arg;
+  const float* w;       // [Bt, ld_pairs]
+  int ld_pairs;
+  int k_first;          // first image of the chunk, as a column of argmax / w
+  int n_img;            // images in the chunk
+  int Bt, T, P, rows, n_st;
+  int hdr_words, block_bytes;
+  int bm_stride;        // words per bitmap row (>= P, odd multiple of... any; conflict-free as long as lanes read consecutive bins)
+  uint8_t* lists;       // [n_img][n_st][block_bytes]
 };
 
-template <> struct PatchFma<24, 2> {
-  __device__ static __forceinline__ void run(float (&acc)[24][2], const uint32_t (&v)[1], uint32_t e, uint32_t ql) {
-    asm volatile(
-        "{\n\t.reg .b16 x0, x1, wl, wh;\n\t"
-        "mov.b32 {x0, x1}, %49;\n\t mov.b32 {wl, wh}, %50;\n\t"
-        "DT: .branchtargets C0, C1, C2, C3, C4, C5, C6, C7, C8, C9, C10, C11, C12, C13, C14, C15, C16, C17, C18, C19, "
-        "C20, C21, C22, C23, DONE;\n\t"
-        "brx.idx.uni %48, DT;\n\t"
-        CXL_F2(0, 0, 1) CXL_F2(1, 2, 3) CXL_F2(2, 4, 5) CXL_F2(3, 6, 7) CXL_F2(4, 8, 9) CXL_F2(5, 10, 11)
-        CXL_F2(6, 12, 13) CXL_F2(7, 14, 15) CXL_F2(8, 16, 17) CXL_F2(9, 18, 19) CXL_F2(10, 20, 21) CXL_F2(11, 22, 23)
-        CXL_F2(12, 24, 25) CXL_F2(13, 26, 27) CXL_F2(14, 28, 29) CXL_F2(15, 30, 31) CXL_F2(16, 32, 33)
-        CXL_F2(17, 34, 35) CXL_F2(18, 36, 37) CXL_F2(19, 38, 39) CXL_F2(20, 40, 41) CXL_F2(21, 42, 43)
-        CXL_F2(22, 44, 45) CXL_F2(23, 46, 47)
-        "DONE:\n\t}"
-        : CXL_A2(0), CXL_A2(1), CXL_A2(2), CXL_A2(3), CXL_A2(4), CXL_A2(5), CXL_A2(6), CXL_A2(7), CXL_A2(8), CXL_A2(9),
-          CXL_A2(10), CXL_A2(11), CXL_A2(12), CXL_A2(13), CXL_A2(14), CXL_A2(15), CXL_A2(16), CXL_A2(17), CXL_A2(18),
-          CXL_A2(19), CXL_A2(20), CXL_A2(21), CXL_A2(22), CXL_A2(23)
-        : "r"(ql), "r"(v[0]), "r"(e));
-  }
-};
-#undef CXL_F4
-#undef CXL_F2
-#undef CXL_A4
-#undef CXL_A2
-
-template <int VEC> struct RowLoad;
-template <> struct RowLoad<4> {
-  __device__ static __forceinline__ void ld(uint32_t addr, uint32_t (&v)[2]) {
-    asm volatile("ld.shared.v2.b32 {%0, %1}, [%2];" : "=r"(v[0]), "=r"(v[1]) : "r"(addr));
-  }
-};
-template <> struct RowLoad<2> {
-  __device__ static __forceinline__ void ld(uint32_t addr, uint32_t (&v)[1]) {
-    asm volatile("ld.shared.b32 %0, [%1];" : "=r"(v[0]) : "r"(addr));
-  }
-};
-
-// Warps [0, nwc): consumers; [nwc, nwc+4): producers (one tile row per lane); nwc+4: TMA issue.
-// Stage = [tile RT x DS bf16][argmax of the tile's rows RT x ES][queues nwc x RT x u32][counts nwc x 4 x u32].
-// Entry = bf16(w) << 16 | row-in-tile << 5 | patch-in-group  (patch-in-group == G: padding, skipped by the dispatch).
-// The host guarantees T >= 8: a tile's RT = 128 rows then span at most 17 texts, i.e. at most two 32-text batches
-// of the per-lane pair-weight cache.
-template <int DS, int G, int C, int MAXW, bool U16>
-__global__ void __launch_bounds__(MAXW * 32, 1)
-maxsim_bwd_dimg_v2_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2Params p) {
-  constexpr int VEC = DS / 32;
-  constexpr int RT = 128;
-  constexpr int NPW = 4;
-  constexpr int ES = U16 ? 2 : 1;
-  constexpr int OFF_SHIFT = (DS == 128) ? 3 : 2;       // (row << 5) -> row * DS * 2 bytes
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
-  V2Barriers* bars = reinterpret_cast<V2Barriers*>(smem + p.stages * p.stage_bytes);
-
+template <bool U16>
+__global__ void __launch_bounds__(128) maxsim_bwd_dimg_lists_kernel(const DimgListParams p) {
+  extern __shared__ uint32_t lsm[];
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int nwc = p.nwc;
-  const int k = blockIdx.x;
-  const bool active = k < p.Bi;                          // cluster padding CTAs run the pipeline but own nothing
-  const int kk = active ? k : p.Bi - 1;
-  const int d0 = blockIdx.y * DS;
-  const int rows = p.rows;
-  const int num_tiles = (rows + RT - 1) / RT;
+  const int per_warp = 16 * p.bm_stride + 256 + kStRows + p.hdr_words;      // words
+  uint32_t* bm = lsm + warp * per_warp;                  // bm[j * bm_stride + q]: bit b = row 32 j + b has argmax q
+  uint16_t* wrow = reinterpret_cast<uint16_t*>(bm + 16 * p.bm_stride);      // bf16 pair weight of each row
+  uint32_t* ent = bm + 16 * p.bm_stride + 256;
+  uint32_t* hdr = ent + kStRows;
+  const long long unit = static_cast<long long>(blockIdx.x) * 4 + warp;
+  if (unit >= static_cast<long long>(p.n_img) * p.n_st) return;
+  const int kl = static_cast<int>(unit / p.n_st);
+  const int s = static_cast<int>(unit % p.n_st);
+  const int kcol = p.k_first + kl;
+  const int rows0 = s * kStRows;
+
+  for (int i = lane; i < 16 * p.bm_stride; i += 32) bm[i] = 0u;
+  __syncwarp();
+
+  // ---- pass A: lane l takes rows [16 l, 16 l + 16): set bitmap bits, record the rows' pair weights ----
+  {
+    const int rl = 16 * lane;
+    const long long g0 = static_cast<long long>(rows0) + rl;                // first global row of this lane
+    uint32_t a[U16 ? 8 : 4];
+#pragma unroll
+    for (int i = 0; i < (U16 ? 8 : 4); ++i) a[i] = 0u;
+    if (g0 < p.ld_arg) {                                                     // ld_arg is a multiple of 16
+      const uint4* src = reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(p.argmax) +
+                                                        (static_cast<size_t>(kcol) * p.ld_arg + g0) * (U16 ? 2 : 1));
+      const uint4 v0 = __ldg(src);
+      a[0] = v0.x; a[1] = v0.y; a[2] = v0.z; a[3] = v0.w;
+      if (U16) {
+        const uint4 v1 = __ldg(src + 1);
+        a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
+      }
+    }
+    int m = static_cast<int>(g0 / p.T);
+    int rem = static_cast<int>(g0 - static_cast<long long>(m) * p.T);
+    float wv = (g0 < p.rows) ? __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol) : 0.f;
+#pragma unroll
+    for (int i = 0; i < 16; ++i) {
+      if (g0 + i < p.rows) {
+        if (rem == p.T) {
+          rem = 0;
+          ++m;
+          wv = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
+        }
+        uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+        q = min(q, static_cast<uint32_t>(p.P - 1));
+        const int r = rl + i;
+        atomicOr(&bm[(r >> 5) * p.bm_stride + q], 1u << (r & 31));
+        wrow[r] = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
+        ++rem;
+      }
+    }
+  }
+  __syncwarp();
+
+  // ---- pass B: per-patch counts -> exclusive prefix -> header ----
+  uint32_t carry = 0;
+  for (int b0 = 0; b0 < p.hdr_words; b0 += 32) {
+    const int b = b0 + lane;
+    uint32_t cnt = 0;
+    if (b < p.P) {
+#pragma unroll
+      for (int j = 0; j < 16; ++j) cnt += __popc(bm[j * p.bm_stride + b]);
+    }
+    uint32_t incl = cnt;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
+      if (lane >= d) incl += up;
+    }
+    if (b < p.hdr_words) hdr[b] = (carry + incl - cnt) | (cnt << 16);
+    carry += __shfl_sync(0xffffffffu, incl, 31);
+  }
+  __syncwarp();
+
+  // ---- pass C: emit the entries of each patch in ascending row order ----
+  for (int b = lane; b < p.P; b += 32) {
+    uint32_t pos = hdr[b] & 0xFFFFu;
+    for (int j = 0; j < 16; ++j) {
+      uint32_t word = bm[j * p.bm_stride + b];
+      while (word != 0u) {
+        const int r = j * 32 + __ffs(word) - 1;
+        word &= word - 1u;
+        ent[pos++] = (static_cast<uint32_t>(wrow[r]) << 16) | static_cast<uint32_t>(r * 128);
+      }
+    }
+  }
+  __syncwarp();
+  // hdr and ent are adjacent in shared memory in the order [ent | hdr]; the block wants [hdr | ent]
+  uint4* dst = reinterpret_cast<uint4*>(p.lists + static_cast<size_t>(unit) * p.block_bytes);
+  const uint4* h4 = reinterpret_cast<const uint4*>(hdr);
+  const uint4* e4 = reinterpret_cast<const uint4*>(ent);
+  const int hq = p.hdr_words / 4;
+  for (int i = lane; i < hq; i += 32) dst[i] = h4[i];
+  for (int i = lane; i < kStRows / 4; i += 32) dst[hq + i] = e4[i];
+}
+
+struct __align__(8) DimgBarriers {
+  uint64_t full[4];
+  uint64_t empty[4];
+};
+
+// Warps [0, NW): consumers (quarter warp o = 4 warp + lane / 8 owns patches [o NPO, o NPO + NPO) of the CTA's NIMG
+// images); warp NW issues the loads.  Stage = [512 x 64 bf16 super-tile of text rows | NIMG list blocks].
+template <int NW, int NPO, int NIMG>
+__global__ void __launch_bounds__((NW + 1) * 32, 1)
+maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2Params p) {
+  constexpr int DS = 64;
+  constexpr uint32_t kTileBytes = kStRows * DS * 2;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 127) & ~uintptr_t(127));
+  DimgBarriers* bars = reinterpret_cast<DimgBarriers*>(smem + p.stages * p.stage_bytes);
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int d0 = blockIdx.x * DS;
+  const int kl0 = blockIdx.y * NIMG;                     // first image of this CTA inside the chunk
+  const int n_st = p.n_st;
   const int stages = p.stages;
   const uint32_t stage_bytes = p.stage_bytes;
-  const uint32_t tile_bytes = p.tile_bytes;
-  const uint32_t a_area = tile_bytes;                    // offsets inside a stage
-  const uint32_t q_area = a_area + RT * ES;
-  const uint32_t c_area = q_area + nwc * RT * 4;
+  const uint32_t block_bytes = p.block_bytes;
   const uint32_t smem0 = smem_u32(smem);
   const uint32_t full0 = smem_u32(&bars->full[0]);
   const uint32_t empty0 = smem_u32(&bars->empty[0]);
-  const uint32_t qfull0 = smem_u32(&bars->qfull[0]);
-  const uint32_t crank = (C > 1) ? cluster_ctarank() : 0;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, nwc);
-      mbar_init(qfull0 + 8 * s, NPW);
-      mbar_init(smem_u32(&bars->ready[s]), C);
+      mbar_init(empty0 + 8 * s, NW);
     }
     fence_barrier_init();
     tma_prefetch_desc(&tmTxt);
   }
   __syncthreads();
-  if (C > 1) cluster_sync_all();
 
-  if (warp == nwc + NPW) {
-    // ===================== TMA issue: text-row tile (multicast) + this image's argmax bytes =====================
+  if (warp == NW) {
     if (lane == 0) {
-      const uint8_t* qsrc = reinterpret_cast<const uint8_t*>(p.argmax) + static_cast<size_t>(p.k_off + kk) * p.ld_arg * ES;
+      const uint8_t* lsrc[NIMG];
+#pragma unroll
+      for (int i = 0; i < NIMG; ++i)
+        lsrc[i] = p.lists + static_cast<size_t>(min(kl0 + i, p.chunk_n - 1)) * n_st * block_bytes;
       int stage = 0;
       uint32_t phase = 0;
-      for (int t = 0; t < num_tiles; ++t) {
+      for (int s = 0; s < n_st; ++s) {
         mbar_wait(empty0 + 8 * stage, phase ^ 1);
         const uint32_t st = smem0 + stage * stage_bytes;
         const uint32_t full = full0 + 8 * stage;
-        const long long avail = p.ld_arg - static_cast<long long>(t) * RT;
-        const uint32_t qbytes = static_cast<uint32_t>((avail < RT ? avail : RT) * ES);
-        mbar_arrive_expect_tx(full, tile_bytes + qbytes);
-        bulk_load_1d(st + a_area, qsrc + static_cast<size_t>(t) * RT * ES, qbytes, full);
-        if (C == 1) {
-          tma_load_2d(st, &tmTxt, full, d0, t * RT);     // rows past the end are zero-filled
-        } else {
-          const uint32_t ready = smem_u32(&bars->ready[stage]);
-          mbar_arrive_cluster(mapa_shared(ready, 0));
-          if (crank == 0) {
-            mbar_wait_cluster(ready, phase);             // every CTA of the cluster freed and armed this stage
-            tma_load_2d_mcast(st, &tmTxt, full, d0, t * RT, static_cast<uint16_t>((1u << C) - 1));
-          }
-        }
+        mbar_arrive_expect_tx(full, kTileBytes + NIMG * block_bytes);
+        tma_load_2d(st, &tmTxt, full, d0, s * kStRows);                          // rows past the end: zero-filled
+        tma_load_2d(st + kTileBytes / 2, &tmTxt, full, d0, s * kStRows + kStRows / 2);
+#pragma unroll
+        for (int i = 0; i < NIMG; ++i)
+          bulk_load_1d(st + kTileBytes + i * block_bytes, lsrc[i] + static_cast<size_t>(s) * block_bytes, block_bytes, full);
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
-  } else if (warp >= nwc) {
-    // ===================== producers: bucket the tile's items by consumer warp =====================
-    const int pw = warp - nwc;
-    const int slot = pw * 32 + lane;
-    const int T = p.T;
-    const float* wcol = p.w + p.k_off + kk;
-    auto load_w = [&](int m) { return m < p.Bt ? __ldg(wcol + static_cast<size_t>(m) * p.ld_pairs) : 0.f; };
-    int m_base = 0;
-    float w_cur = load_w(lane), w_nxt = load_w(32 + lane);
-    int m_row = slot / T;                                // text of this lane's row in the current tile
-    int n_row = slot - m_row * T;
-    int m_first = 0, n_first = 0;                        // text / token of the tile's first row (warp-uniform)
-    const uint32_t lt_mask = (1u << lane) - 1;
-    const uint32_t q_max = static_cast<uint32_t>(p.P - 1);
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int t = 0; t < num_tiles; ++t) {
-      while (m_first >= m_base + 32) {                   // keep the tile's first text inside w_cur
-        m_base += 32;
-        w_cur = w_nxt;
-        w_nxt = load_w(m_base + 32 + lane);
-      }
-      const int mi = min(m_row, p.Bt - 1) - m_base;      // 0 .. 63
-      const float wa = __shfl_sync(0xffffffffu, w_cur, mi & 31);
-      const float wb = __shfl_sync(0xffffffffu, w_nxt, mi & 31);
-      const float wv = mi < 32 ? wa : wb;
-      const bool valid = t * RT + slot < rows;
-      const uint32_t st = smem0 + stage * stage_bytes;
-      mbar_wait(full0 + 8 * stage, phase);               // tile + argmax bytes have landed
-      uint32_t q;
-      if (U16) asm volatile("ld.shared.u16 %0, [%1];" : "=r"(q) : "r"(st + a_area + slot * ES));
-      else asm volatile("ld.shared.u8 %0, [%1];" : "=r"(q) : "r"(st + a_area + slot * ES));
-      q = min(q, q_max);
-      const uint32_t g = (G == 8) ? (q >> 3) : ((q * 2731u) >> 16);
-      const uint32_t ql = q - g * G;
-      const uint32_t mask = __match_any_sync(0xffffffffu, valid ? g : 0xFFFFu);
-      const uint32_t rank = __popc(mask & lt_mask);
-      if (lane < nwc) sts32(st + c_area + (lane * 4 + pw) * 4, 0u);
-      __syncwarp();
-      if (valid && rank == 0) sts32(st + c_area + (g * 4 + pw) * 4, __popc(mask));
-      named_bar_sync(1, NPW * 32);
-      if (valid) {
-        uint32_t base = rank;
-        for (int pp = 0; pp < pw; ++pp) {
-          uint32_t c;
-          asm volatile("ld.shared.b32 %0, [%1];" : "=r"(c) : "r"(st + c_area + (g * 4 + pp) * 4));
-          base += c;
-        }
-        sts32(st + q_area + (g * RT + base) * 4, pack_entry(wv, (static_cast<uint32_t>(slot) << 5) | ql));
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(qfull0 + 8 * stage);
-      n_row += RT;
-      while (n_row >= T) { n_row -= T; ++m_row; }
-      n_first += RT;
-      while (n_first >= T) { n_first -= T; ++m_first; }
-      if (++stage == stages) { stage = 0; phase ^= 1; }
-    }
-  } else {
-    // ===================== consumer warp `warp` owns patches [warp*G, warp*G + G) =====================
-    float acc[G][VEC];
+    return;
+  }
+
+  float acc[NIMG][NPO][8];
 #pragma unroll
-    for (int j = 0; j < G; ++j)
+  for (int i = 0; i < NIMG; ++i)
 #pragma unroll
-      for (int i = 0; i < VEC; ++i) acc[j][i] = 0.f;
-    const uint32_t lane_off = lane * VEC * 2;
-    const uint32_t my_q = q_area + warp * (RT * 4);
-    const uint32_t my_c = c_area + warp * 16;
-    int stage = 0;
-    uint32_t phase = 0;
-    for (int t = 0; t < num_tiles; ++t) {
-      const uint32_t st = smem0 + stage * stage_bytes;
-      mbar_wait(qfull0 + 8 * stage, phase);              // queues ready (the producers saw the data land)
-      mbar_wait(full0 + 8 * stage, phase);               // observe the TMA completion ourselves (already done)
-      const uint4 c4 = lds128(st + my_c);
-      const int n = static_cast<int>(c4.x + c4.y + c4.z + c4.w);
-      const uint32_t qa = st + my_q;
-      const uint32_t stl = st + lane_off;
-      for (int i = 0; i < n; i += 4) {
-        const uint4 e4 = lds128(qa + i * 4);
-        const uint32_t e[4] = {e4.x, e4.y, e4.z, e4.w};
+    for (int j = 0; j < NPO; ++j)
 #pragma unroll
-        for (int u = 0; u < 4; ++u) {
-          const uint32_t eu = (u == 0 || i + u < n) ? e[u] : static_cast<uint32_t>(G);   // row 0, weight +0, skipped
-          uint32_t v[VEC / 2];
-          RowLoad<VEC>::ld(stl + ((eu & 0xFFE0u) << OFF_SHIFT), v);
-          PatchFma<G, VEC>::run(acc, v, eu, eu & 31u);
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(empty0 + 8 * stage);
-      if (++stage == stages) { stage = 0; phase ^= 1; }
-    }
-    if (active) {
+      for (int c = 0; c < 8; ++c) acc[i][j][c] = 0.f;
+  const int owner = warp * 4 + (lane >> 3);
+  const uint32_t lane_off = (lane & 7) * 16;
+  const uint32_t hdr_bytes = p.hdr_words * 4;
+  int stage = 0;
+  uint32_t phase = 0;
+  for (int s = 0; s < n_st; ++s) {
+    const uint32_t st = smem0 + stage * stage_bytes;
+    mbar_wait(full0 + 8 * stage, phase);
+    const uint32_t row_base = st + lane_off;
 #pragma unroll
-      for (int j = 0; j < G; ++j) {
-        const int q = warp * G + j;
-        if (q < p.P) {
-          float* o = p.dimg + (static_cast<size_t>(k) * p.P + q) * p.D + d0 + lane * VEC;
+    for (int i = 0; i < NIMG; ++i) {
+      const uint32_t blk = st + kTileBytes + i * block_bytes;
 #pragma unroll
-          for (int i = 0; i < VEC; i += 2) {
-            float2 val = make_float2(acc[j][i], acc[j][i + 1]);
-            if (p.accumulate_img) {
-              const float2 old = *reinterpret_cast<const float2*>(o + i);
-              val.x += old.x;
-              val.y += old.y;
-            }
-            *reinterpret_cast<float2*>(o + i) = val;
+      for (int j = 0; j < NPO; ++j) {
+        uint32_t h;
+        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(h) : "r"(blk + (owner * NPO + j) * 4));
+        const int len = static_cast<int>(h >> 16);
+        const uint32_t e0 = blk + hdr_bytes + (h & 0xFFFFu) * 4;
+        const int maxlen = __reduce_max_sync(0xffffffffu, len);
+#pragma unroll 2
+        for (int it = 0; it < maxlen; ++it) {
+          if (it < len) {
+            uint32_t e;
+            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(e) : "r"(e0 + it * 4));
+            const uint4 v = lds128(row_base + (e & 0xFFFFu));
+            fhfma8(acc[i][j], v, e);
           }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+    if (++stage == stages) { stage = 0; phase ^= 1; }
+  }
+#pragma unroll
+  for (int i = 0; i < NIMG; ++i) {
+    const int kl = kl0 + i;
+    if (kl < p.chunk_n) {
+#pragma unroll
+      for (int j = 0; j < NPO; ++j) {
+        const int q = owner * NPO + j;
+        if (q < p.P) {
+          float* o = p.dimg + (static_cast<size_t>(p.chunk_k0 + kl) * p.P + q) * p.D + d0 + (lane & 7) * 8;
+          float4 lo = make_float4(acc[i][j][0], acc[i][j][1], acc[i][j][2], acc[i][j][3]);
+          float4 hi = make_float4(acc[i][j][4], acc[i][j][5], acc[i][j][6], acc[i][j][7]);
+          if (p.accumulate_img) {
+            const float4 a = *reinterpret_cast<const float4*>(o);
+            const float4 b = *reinterpret_cast<const float4*>(o + 4);
+            lo.x += a.x; lo.y += a.y; lo.z += a.z; lo.w += a.w;
+            hi.x += b.x; hi.y += b.y; hi.z += b.z; hi.w += b.w;
+          }
+          *reinterpret_cast<float4*>(o) = lo;
+          *reinterpret_cast<float4*>(o + 4) = hi;
         }
       }
     }
   }
-  if (C > 1) cluster_sync_all();
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -539,37 +539,45 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
   return CXL_OK;
 }
 
-template <int DS, int G, int C, int MAXW, bool U16>
-static int launch_dimg_v2(const void* txt, BwdV2Params p, int max_smem, cudaStream_t stream) {
-  constexpr int RT = 128;
-  p.nwc = (p.P + G - 1) / G;
-  if (p.nwc + 5 > MAXW) return CXL_ERR_UNSUPPORTED;
-  p.tile_bytes = RT * DS * 2;
-  p.stage_bytes = round_up_i(p.tile_bytes + RT * (U16 ? 2 : 1) + p.nwc * RT * 4 + p.nwc * 16, 128);
-  const int overhead = 128 + static_cast<int>(sizeof(V2Barriers));
+// One chunk of images: lists pre-pass, then the gather kernel.  `p.lists` is scratch for chunk_cap images.
+template <int NW, int NPO, int NIMG>
+static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chunk_cap, cudaStream_t stream) {
+  constexpr int DS = 64;
+  p.stage_bytes = kStRows * DS * 2 + NIMG * p.block_bytes;
+  const int overhead = 128 + static_cast<int>(sizeof(DimgBarriers));
   int stages = (max_smem - overhead) / p.stage_bytes;
   if (stages < 2) return CXL_ERR_UNSUPPORTED;
-  p.stages = stages > 6 ? 6 : stages;
+  p.stages = stages > 4 ? 4 : stages;
   const int smem_bytes = overhead + p.stages * p.stage_bytes;
   CUtensorMap tm;
-  int rc = make_tmap_plain(&tm, txt, p.rows, p.D, DS, RT);
+  int rc = make_tmap_plain(&tm, txt, p.rows, p.D, DS, kStRows / 2);
   if (rc != CXL_OK) return rc;
-  auto kern = maxsim_bwd_dimg_v2_kernel<DS, G, C, MAXW, U16>;
+  auto kern = maxsim_bwd_dimg_v3_kernel<NW, NPO, NIMG>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  cudaLaunchConfig_t cfg;
-  memset(&cfg, 0, sizeof(cfg));
-  cfg.gridDim = dim3(round_up_i(p.Bi, C), p.D / DS);
-  cfg.blockDim = dim3((p.nwc + 5) * 32);
-  cfg.dynamicSmemBytes = smem_bytes;
-  cfg.stream = stream;
-  cudaLaunchAttribute attr[1];
-  attr[0].id = cudaLaunchAttributeClusterDimension;
-  attr[0].val.clusterDim.x = C;
-  attr[0].val.clusterDim.y = 1;
-  attr[0].val.clusterDim.z = 1;
-  cfg.attrs = attr;
-  cfg.numAttrs = 1;
-  CXL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tm, p));
+
+  DimgListParams lp;
+  lp.argmax = p.argmax; lp.ld_arg = p.ld_arg; lp.w = p.w; lp.ld_pairs = p.ld_pairs;
+  lp.Bt = p.Bt; lp.T = p.T; lp.P = p.P; lp.rows = p.rows; lp.n_st = p.n_st;
+  lp.hdr_words = p.hdr_words; lp.block_bytes = p.block_bytes;
+  lp.bm_stride = round_up_i(p.P, 4);
+  lp.lists = const_cast<uint8_t*>(p.lists);
+  const int lists_smem = 4 * (16 * lp.bm_stride + 256 + kStRows + lp.hdr_words) * 4;
+  auto lkern = p.argmax_u16 ? maxsim_bwd_dimg_lists_kernel<true> : maxsim_bwd_dimg_lists_kernel<false>;
+  CXL_CUDA_CHECK(cudaFuncSetAttribute(lkern, cudaFuncAttributeMaxDynamicSharedMemorySize, lists_smem));
+
+  for (int k0 = 0; k0 < p.Bi; k0 += chunk_cap) {
+    const int n = (p.Bi - k0 < chunk_cap) ? p.Bi - k0 : chunk_cap;
+    lp.k_first = p.k_off + k0;
+    lp.n_img = n;
+    const long long units = static_cast<long long>(n) * p.n_st;
+    lkern<<<static_cast<unsigned>((units + 3) / 4), 128, lists_smem, stream>>>(lp);
+    CXL_CUDA_CHECK(cudaGetLastError());
+    p.chunk_k0 = k0;
+    p.chunk_n = n;
+    dim3 grid(p.D / DS, (n + NIMG - 1) / NIMG);
+    kern<<<grid, (NW + 1) * 32, smem_bytes, stream>>>(tm, p);
+    CXL_CUDA_CHECK(cudaGetLastError());
+  }
   return CXL_OK;
 }
 
@@ -602,17 +610,38 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     if (rc != CXL_OK) return rc;
   }
   if (dimg != nullptr) {
-    static const int cluster = env_int("CXL_DIMG_CLUSTER", 2);
-    if (P <= 25 * 8) {
-      if (cluster >= 4) rc = launch_dimg_v2<128, 8, 4, 30, false>(txt, p, max_smem, stream);
-      else if (cluster >= 2) rc = launch_dimg_v2<128, 8, 2, 30, false>(txt, p, max_smem, stream);
-      else rc = launch_dimg_v2<128, 8, 1, 30, false>(txt, p, max_smem, stream);
-    } else if (P <= 256) {
-      if (cluster >= 2) rc = launch_dimg_v2<64, 24, 2, 29, false>(txt, p, max_smem, stream);
-      else rc = launch_dimg_v2<64, 24, 1, 29, false>(txt, p, max_smem, stream);
+    // variant: consumer warps x patches per quarter warp x images per CTA
+    const int npo = P <= 200 ? 2 : P <= 300 ? 3 : 8;
+    const int nw = P <= 300 ? 25 : 19;
+    const int nimg = P <= 200 ? 2 : 1;
+    p.n_st = (p.rows + kStRows - 1) / kStRows;
+    p.hdr_words = round_up_i(nw * 4 * npo, 32);
+    p.block_bytes = p.hdr_words * 4 + kStRows * 4;
+    // scratch for the row lists of one chunk of images (stream-ordered allocation)
+    static const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4096);
+    const long long per_img = static_cast<long long>(p.n_st) * p.block_bytes;
+    long long cap = (static_cast<long long>(scratch_mb) << 20) / per_img;
+    if (cap >= Bi) {
+      cap = Bi;
     } else {
-      if (cluster >= 2) rc = launch_dimg_v2<64, 24, 2, 29, true>(txt, p, max_smem, stream);
-      else rc = launch_dimg_v2<64, 24, 1, 29, true>(txt, p, max_smem, stream);
+      // whole waves: the gather kernel runs D/64 CTAs per image group, one CTA per SM
+      int sms = 148;
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      const long long per_wave = static_cast<long long>(sms) * nimg;           // images per (D/64) waves
+      if (cap >= per_wave) cap = cap / per_wave * per_wave;
+      cap = cap / nimg * nimg;
+      if (cap < nimg) cap = nimg;
+    }
+    void* scratch = nullptr;
+    CXL_CUDA_CHECK(cudaMallocAsync(&scratch, static_cast<size_t>(cap * per_img), stream));
+    p.lists = static_cast<const uint8_t*>(scratch);
+    if (npo == 2) rc = launch_dimg_v3<25, 2, 2>(txt, p, max_smem, static_cast<int>(cap), stream);
+    else if (npo == 3) rc = launch_dimg_v3<25, 3, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
+    else rc = launch_dimg_v3<19, 8, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
+    const cudaError_t fe = cudaFreeAsync(scratch, stream);
+    if (rc == CXL_OK && fe != cudaSuccess) {
+      set_cuda_error(fe, "cudaFreeAsync (dImg lists)");
+      rc = CXL_ERR_CUDA;
     }
     if (rc != CXL_OK) return rc;
   }
