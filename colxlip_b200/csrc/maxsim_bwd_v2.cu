@@ -67,6 +67,19 @@ __device__ __forceinline__ void fhfma8(float (&a)[8], const uint4& v, uint32_t e
       : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e));
 }
 
+// same, weight in the low half of e
+__device__ __forceinline__ void fhfma8_lo(float (&a)[8], const uint4& v, uint32_t e) {
+  asm("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"
+      "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"
+      "mov.b32 {wl, wh}, %12;\n\t"
+      "fma.rn.f32.bf16 %0, x0, wl, %0;\n\t fma.rn.f32.bf16 %1, x1, wl, %1;\n\t"
+      "fma.rn.f32.bf16 %2, x2, wl, %2;\n\t fma.rn.f32.bf16 %3, x3, wl, %3;\n\t"
+      "fma.rn.f32.bf16 %4, x4, wl, %4;\n\t fma.rn.f32.bf16 %5, x5, wl, %5;\n\t"
+      "fma.rn.f32.bf16 %6, x6, wl, %6;\n\t fma.rn.f32.bf16 %7, x7, wl, %7;\n\t}"
+      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])
+      : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e));
+}
+
 __device__ __forceinline__ uint4 lds128(uint32_t addr) {
   uint4 v;
   asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
@@ -227,11 +240,12 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
 // branch costs far more than the item's FMAs): a quarter warp owns NPO patches of NIMG images for one 64-wide D
 // slice and walks the list of text rows whose argmax is that patch.  The lists come from a cheap pre-pass
 // (one warp per (image, 512-row super-tile)): a deterministic counting sort of the super-tile's rows by patch.
+// Lock-step padding of the four quarter warps uses a dummy entry: row 0 with weight +0.
 //
 // List block of one (image, super-tile), `block_bytes` long:
 //   u32 hdr[hdr_words]   hdr[q] = first entry | number of entries << 16   (zero for q >= P)
 //   u32 ent[512]         entries grouped by patch, ascending row inside a patch;
-//                        entry = bf16(w) << 16 | row-in-super-tile * 128   (byte offset of the row in the tile)
+//                        entry = row-in-super-tile * 128 << 16 | bf16(w)   (high half: byte offset of the row in the tile)
 constexpr int kStRows = 512;
 
 struct DimgListParams {
@@ -243,31 +257,34 @@ struct DimgListParams {
   int n_img;            // images in the chunk
   int Bt, T, P, rows, n_st;
   int hdr_words, block_bytes;
-  int bm_stride;        // words per bitmap row (>= P, odd multiple of... any; conflict-free as long as lanes read consecutive bins)
   uint8_t* lists;       // [n_img][n_st][block_bytes]
 };
 
 template <bool U16>
-__global__ void __launch_bounds__(128) maxsim_bwd_dimg_lists_kernel(const DimgListParams p) {
+__global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgListParams p) {
   extern __shared__ uint32_t lsm[];
+  constexpr int kArgWords = U16 ? 256 : 128;
   const int warp = threadIdx.x >> 5;
   const int lane = threadIdx.x & 31;
-  const int per_warp = 16 * p.bm_stride + 256 + kStRows + p.hdr_words;      // words
-  uint32_t* bm = lsm + warp * per_warp;                  // bm[j * bm_stride + q]: bit b = row 32 j + b has argmax q
-  uint16_t* wrow = reinterpret_cast<uint16_t*>(bm + 16 * p.bm_stride);      // bf16 pair weight of each row
-  uint32_t* ent = bm + 16 * p.bm_stride + 256;
-  uint32_t* hdr = ent + kStRows;
-  const long long unit = static_cast<long long>(blockIdx.x) * 4 + warp;
+  const int per_warp = 2 * p.hdr_words + kStRows + kArgWords + 256;      // words
+  uint32_t* cur = lsm + warp * per_warp;                 // per-patch count, then fill cursor
+  uint32_t* hdr = cur + p.hdr_words;
+  uint32_t* ent = hdr + p.hdr_words;
+  uint32_t* arg_w = ent + kStRows;                       // the super-tile's argmax values, row order
+  uint16_t* wrow = reinterpret_cast<uint16_t*>(arg_w + kArgWords);          // bf16 pair weight of each row
+  const long long unit = static_cast<long long>(blockIdx.x) * 8 + warp;
   if (unit >= static_cast<long long>(p.n_img) * p.n_st) return;
   const int kl = static_cast<int>(unit / p.n_st);
   const int s = static_cast<int>(unit % p.n_st);
   const int kcol = p.k_first + kl;
   const int rows0 = s * kStRows;
+  const int nrows = min(kStRows, p.rows - rows0);
+  const uint32_t q_max = static_cast<uint32_t>(p.P - 1);
 
-  for (int i = lane; i < 16 * p.bm_stride; i += 32) bm[i] = 0u;
+  for (int i = lane; i < p.hdr_words; i += 32) cur[i] = 0u;
   __syncwarp();
 
-  // ---- pass A: lane l takes rows [16 l, 16 l + 16): set bitmap bits, record the rows' pair weights ----
+  // ---- pass A: lane l takes rows [16 l, 16 l + 16): count per patch, stage argmax + pair weights in row order ----
   {
     const int rl = 16 * lane;
     const long long g0 = static_cast<long long>(rows0) + rl;                // first global row of this lane
@@ -284,62 +301,74 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_lists_kernel(const DimgLi
         a[4] = v1.x; a[5] = v1.y; a[6] = v1.z; a[7] = v1.w;
       }
     }
+    uint4* adst = reinterpret_cast<uint4*>(arg_w) + lane * (U16 ? 2 : 1);
+    adst[0] = make_uint4(a[0], a[1], a[2], a[3]);
+    if (U16) adst[1] = make_uint4(a[4], a[5], a[6], a[7]);
     int m = static_cast<int>(g0 / p.T);
     int rem = static_cast<int>(g0 - static_cast<long long>(m) * p.T);
     float wv = (g0 < p.rows) ? __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol) : 0.f;
+    uint32_t wpk[8];
 #pragma unroll
     for (int i = 0; i < 16; ++i) {
-      if (g0 + i < p.rows) {
+      uint32_t wb = 0u;
+      if (rl + i < nrows) {
         if (rem == p.T) {
           rem = 0;
           ++m;
           wv = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
         }
-        uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
-        q = min(q, static_cast<uint32_t>(p.P - 1));
-        const int r = rl + i;
-        atomicOr(&bm[(r >> 5) * p.bm_stride + q], 1u << (r & 31));
-        wrow[r] = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
         ++rem;
+        const uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+        atomicAdd(&cur[min(q, q_max)], 1u);
+        wb = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
       }
+      if (i & 1) wpk[i >> 1] |= wb << 16;
+      else wpk[i >> 1] = wb;
     }
+    uint4* wdst = reinterpret_cast<uint4*>(wrow) + lane * 2;
+    wdst[0] = make_uint4(wpk[0], wpk[1], wpk[2], wpk[3]);
+    wdst[1] = make_uint4(wpk[4], wpk[5], wpk[6], wpk[7]);
   }
   __syncwarp();
 
-  // ---- pass B: per-patch counts -> exclusive prefix -> header ----
+  // ---- pass B: exclusive prefix of the counts -> header, fill cursors ----
   uint32_t carry = 0;
   for (int b0 = 0; b0 < p.hdr_words; b0 += 32) {
     const int b = b0 + lane;
-    uint32_t cnt = 0;
-    if (b < p.P) {
-#pragma unroll
-      for (int j = 0; j < 16; ++j) cnt += __popc(bm[j * p.bm_stride + b]);
-    }
+    const uint32_t cnt = cur[b];
     uint32_t incl = cnt;
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) {
       const uint32_t up = __shfl_up_sync(0xffffffffu, incl, d);
       if (lane >= d) incl += up;
     }
-    if (b < p.hdr_words) hdr[b] = (carry + incl - cnt) | (cnt << 16);
+    const uint32_t start = carry + incl - cnt;
+    hdr[b] = start | (cnt << 16);
+    cur[b] = start;
     carry += __shfl_sync(0xffffffffu, incl, 31);
   }
   __syncwarp();
 
-  // ---- pass C: emit the entries of each patch in ascending row order ----
-  for (int b = lane; b < p.P; b += 32) {
-    uint32_t pos = hdr[b] & 0xFFFFu;
-    for (int j = 0; j < 16; ++j) {
-      uint32_t word = bm[j * p.bm_stride + b];
-      while (word != 0u) {
-        const int r = j * 32 + __ffs(word) - 1;
-        word &= word - 1u;
-        ent[pos++] = (static_cast<uint32_t>(wrow[r]) << 16) | static_cast<uint32_t>(r * 128);
-      }
+  // ---- pass C: place the entries, 32 consecutive rows per round; lanes with the same patch are ranked by
+  //      lane (= row) order, so every list comes out in ascending row order whatever the scheduling ----
+  const uint32_t lt_mask = (1u << lane) - 1;
+  const uint8_t* arg8 = reinterpret_cast<const uint8_t*>(arg_w);
+  const uint16_t* arg16 = reinterpret_cast<const uint16_t*>(arg_w);
+  for (int r = lane; r < ((nrows + 31) & ~31); r += 32) {
+    const bool valid = r < nrows;
+    const uint32_t q = min(static_cast<uint32_t>(U16 ? arg16[r] : arg8[r]), q_max);
+    const uint32_t mask = __match_any_sync(0xffffffffu, valid ? q : 0xFFFFFFFFu);
+    const uint32_t rank = __popc(mask & lt_mask);
+    const int leader = __ffs(mask) - 1;
+    uint32_t base = 0;
+    if (valid && rank == 0) {
+      base = cur[q];
+      cur[q] = base + __popc(mask);
     }
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (valid) ent[base + rank] = (static_cast<uint32_t>(r * 128) << 16) | static_cast<uint32_t>(wrow[r]);
+    __syncwarp();
   }
-  __syncwarp();
-  // hdr and ent are adjacent in shared memory in the order [ent | hdr]; the block wants [hdr | ent]
   uint4* dst = reinterpret_cast<uint4*>(p.lists + static_cast<size_t>(unit) * p.block_bytes);
   const uint4* h4 = reinterpret_cast<const uint4*>(hdr);
   const uint4* e4 = reinterpret_cast<const uint4*>(ent);
@@ -435,14 +464,18 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
         const int len = static_cast<int>(h >> 16);
         const uint32_t e0 = blk + hdr_bytes + (h & 0xFFFFu) * 4;
         const int maxlen = __reduce_max_sync(0xffffffffu, len);
-#pragma unroll 2
-        for (int it = 0; it < maxlen; ++it) {
-          if (it < len) {
-            uint32_t e;
-            asm volatile("ld.shared.b32 %0, [%1];" : "=r"(e) : "r"(e0 + it * 4));
-            const uint4 v = lds128(row_base + (e & 0xFFFFu));
-            fhfma8(acc[i][j], v, e);
-          }
+        for (int it = 0; it < maxlen; it += 2) {
+          // dummy entry past the end of this quarter's list: row 0 with weight +0
+          uint32_t ea, eb;
+          asm volatile("{\n\t.reg .pred pa, pb;\n\t"
+                       "setp.lt.s32 pa, %3, %4;\n\t setp.lt.s32 pb, %5, %4;\n\t"
+                       "mov.b32 %0, 0;\n\t mov.b32 %1, 0;\n\t"
+                       "@pa ld.shared.b32 %0, [%2];\n\t @pb ld.shared.b32 %1, [%2+4];\n\t}"
+                       : "=&r"(ea), "=&r"(eb) : "r"(e0 + it * 4), "r"(it), "r"(len), "r"(it + 1));
+          const uint4 va = lds128(row_base + (ea >> 16));
+          const uint4 vb = lds128(row_base + (eb >> 16));
+          fhfma8_lo(acc[i][j], va, ea);
+          fhfma8_lo(acc[i][j], vb, eb);
         }
       }
     }
@@ -543,7 +576,7 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
 template <int NW, int NPO, int NIMG>
 static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chunk_cap, cudaStream_t stream) {
   constexpr int DS = 64;
-  p.stage_bytes = kStRows * DS * 2 + NIMG * p.block_bytes;
+  p.stage_bytes = kStRows * DS * 2 + NIMG * p.block_bytes;           // tile | list blocks
   const int overhead = 128 + static_cast<int>(sizeof(DimgBarriers));
   int stages = (max_smem - overhead) / p.stage_bytes;
   if (stages < 2) return CXL_ERR_UNSUPPORTED;
@@ -559,9 +592,8 @@ static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chun
   lp.argmax = p.argmax; lp.ld_arg = p.ld_arg; lp.w = p.w; lp.ld_pairs = p.ld_pairs;
   lp.Bt = p.Bt; lp.T = p.T; lp.P = p.P; lp.rows = p.rows; lp.n_st = p.n_st;
   lp.hdr_words = p.hdr_words; lp.block_bytes = p.block_bytes;
-  lp.bm_stride = round_up_i(p.P, 4);
   lp.lists = const_cast<uint8_t*>(p.lists);
-  const int lists_smem = 4 * (16 * lp.bm_stride + 256 + kStRows + lp.hdr_words) * 4;
+  const int lists_smem = 8 * (2 * lp.hdr_words + kStRows + (p.argmax_u16 ? 256 : 128) + 256) * 4;
   auto lkern = p.argmax_u16 ? maxsim_bwd_dimg_lists_kernel<true> : maxsim_bwd_dimg_lists_kernel<false>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(lkern, cudaFuncAttributeMaxDynamicSharedMemorySize, lists_smem));
 
@@ -570,7 +602,7 @@ static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chun
     lp.k_first = p.k_off + k0;
     lp.n_img = n;
     const long long units = static_cast<long long>(n) * p.n_st;
-    lkern<<<static_cast<unsigned>((units + 3) / 4), 128, lists_smem, stream>>>(lp);
+    lkern<<<static_cast<unsigned>((units + 7) / 8), 256, lists_smem, stream>>>(lp);
     CXL_CUDA_CHECK(cudaGetLastError());
     p.chunk_k0 = k0;
     p.chunk_n = n;
@@ -631,6 +663,14 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
       if (cap >= per_wave) cap = cap / per_wave * per_wave;
       cap = cap / nimg * nimg;
       if (cap < nimg) cap = nimg;
+    }
+    static bool pool_set[64] = {false};
+    if (dev < 64 && !pool_set[dev]) {           // keep freed scratch cached in the device's pool between calls
+      cudaMemPool_t pool;
+      CXL_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
+      unsigned long long keep = ~0ull;
+      CXL_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+      pool_set[dev] = true;
     }
     void* scratch = nullptr;
     CXL_CUDA_CHECK(cudaMallocAsync(&scratch, static_cast<size_t>(cap * per_img), stream));
