@@ -454,24 +454,31 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
     const uint32_t st = smem0 + stage * stage_bytes;
     mbar_wait(full0 + 8 * stage, phase);
     const uint32_t row_base = st + lane_off;
+    // headers of this quarter warp's NIMG x NPO lists first (their latency overlaps), then the lists
+    uint32_t h[NIMG][NPO];
+#pragma unroll
+    for (int i = 0; i < NIMG; ++i)
+#pragma unroll
+      for (int j = 0; j < NPO; ++j)
+        asm volatile("ld.shared.b32 %0, [%1];"
+                     : "=r"(h[i][j]) : "r"(st + kTileBytes + i * block_bytes + (owner * NPO + j) * 4));
 #pragma unroll
     for (int i = 0; i < NIMG; ++i) {
-      const uint32_t blk = st + kTileBytes + i * block_bytes;
+      const uint32_t ent = st + kTileBytes + i * block_bytes + hdr_bytes;
 #pragma unroll
       for (int j = 0; j < NPO; ++j) {
-        uint32_t h;
-        asm volatile("ld.shared.b32 %0, [%1];" : "=r"(h) : "r"(blk + (owner * NPO + j) * 4));
-        const int len = static_cast<int>(h >> 16);
-        const uint32_t e0 = blk + hdr_bytes + (h & 0xFFFFu) * 4;
+        const int len = static_cast<int>(h[i][j] >> 16);
+        uint32_t ep = ent + (h[i][j] & 0xFFFFu) * 4;
         const int maxlen = __reduce_max_sync(0xffffffffu, len);
-        for (int it = 0; it < maxlen; it += 2) {
+#pragma unroll 1
+        for (int it = 0; it < maxlen; it += 2, ep += 8) {
           // dummy entry past the end of this quarter's list: row 0 with weight +0
           uint32_t ea, eb;
           asm volatile("{\n\t.reg .pred pa, pb;\n\t"
                        "setp.lt.s32 pa, %3, %4;\n\t setp.lt.s32 pb, %5, %4;\n\t"
                        "mov.b32 %0, 0;\n\t mov.b32 %1, 0;\n\t"
                        "@pa ld.shared.b32 %0, [%2];\n\t @pb ld.shared.b32 %1, [%2+4];\n\t}"
-                       : "=&r"(ea), "=&r"(eb) : "r"(e0 + it * 4), "r"(it), "r"(len), "r"(it + 1));
+                       : "=&r"(ea), "=&r"(eb) : "r"(ep), "r"(it), "r"(len), "r"(it + 1));
           const uint4 va = lds128(row_base + (ea >> 16));
           const uint4 vb = lds128(row_base + (eb >> 16));
           fhfma8_lo(acc[i][j], va, ea);
