@@ -226,7 +226,8 @@ def run_gpu(args):
     barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
-    l0 = CudaKernels.launches
+    from colxlip_b200.kernels import default_kernels
+    l0 = default_kernels().launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e0.record()
     for _ in range(args.steps):
@@ -234,7 +235,7 @@ def run_gpu(args):
     e1.record()
     barrier()
     clocks = sampler.stop()
-    launches = CudaKernels.launches - l0
+    launches = default_kernels().launches() - l0     # our kernels inside the timed region (this rank)
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)

@@ -7,7 +7,7 @@ from __future__ import annotations
 
 import ctypes
 import os
-from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_void_p
+from ctypes import c_char_p, c_float, c_int, c_longlong, c_size_t, c_ulonglong, c_void_p
 from typing import Optional
 
 _PKG = os.path.dirname(os.path.abspath(__file__))
@@ -24,6 +24,7 @@ _lib: Optional[ctypes.CDLL] = None
 _FP = ctypes.POINTER(c_float)
 SYMBOLS = {
     "cxl_strerror": (c_char_p, [c_int]),
+    "cxl_kernel_launches": (c_ulonglong, []),
     "cxl_last_cuda_error": (c_char_p, []),
     "cxl_version": (c_int, []),
     "cxl_device_check": (c_int, []),

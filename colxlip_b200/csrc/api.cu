@@ -12,6 +12,10 @@ void set_cuda_error(cudaError_t e, const char* where) {
   snprintf(g_cuda_err, sizeof(g_cuda_err), "%s: %s (%s)", where, cudaGetErrorName(e), cudaGetErrorString(e));
 }
 
+static unsigned long long g_launches = 0;
+void note_launch() { __atomic_fetch_add(&g_launches, 1ull, __ATOMIC_RELAXED); }
+unsigned long long launches_so_far() { return __atomic_load_n(&g_launches, __ATOMIC_RELAXED); }
+
 int num_sms() {
   static int cached[64] = {0};
   int dev = 0;
@@ -58,6 +62,8 @@ static int device_ok() {
 using namespace cxl;
 
 extern "C" {
+
+unsigned long long cxl_kernel_launches(void) { return cxl::launches_so_far(); }
 
 const char* cxl_strerror(int code) {
   switch (code) {

@@ -26,6 +26,10 @@ void set_cuda_error(cudaError_t e, const char* where);
 
 int num_sms();
 
+// every kernel launch of the library goes through CXL_COUNTED(stream): cxl_kernel_launches() reports the total
+void note_launch();
+#define CXL_COUNTED(stream) (::cxl::note_launch(), (stream))
+
 // ---- small device utilities -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void* p) {
   return static_cast<uint32_t>(__cvta_generic_to_shared(p));

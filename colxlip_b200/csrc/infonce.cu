@@ -149,12 +149,12 @@ int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int 
   const int nblk = (B_loc + kColRowsPerBlock - 1) / kColRowsPerBlock;
   float* pmax = reinterpret_cast<float*>(ws);
   float* psum = pmax + static_cast<size_t>(nblk) * B;
-  infonce_row_kernel<<<B_loc, 256, 0, stream>>>(X, scale_dev, B, row0, row_lse, diag);
+  infonce_row_kernel<<<B_loc, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B, row0, row_lse, diag);
   CXL_CUDA_CHECK(cudaGetLastError());
   dim3 g((B + 511) / 512, nblk);
-  infonce_col_partial_kernel<<<g, 128, 0, stream>>>(X, scale_dev, B_loc, B, pmax, psum);
+  infonce_col_partial_kernel<<<g, 128, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B_loc, B, pmax, psum);
   CXL_CUDA_CHECK(cudaGetLastError());
-  infonce_col_combine_kernel<<<(B + 255) / 256, 256, 0, stream>>>(pmax, psum, nblk, B, col_max, col_sum);
+  infonce_col_combine_kernel<<<(B + 255) / 256, 256, 0, CXL_COUNTED(stream)>>>(pmax, psum, nblk, B, col_max, col_sum);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }
@@ -177,7 +177,7 @@ int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, 
   int gx = (B + 256 * 8 - 1) / (256 * 8);
   if (gx < 1) gx = 1;
   dim3 g(gx, B_loc);
-  infonce_grad_kernel<<<g, 256, 0, stream>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX,
+  infonce_grad_kernel<<<g, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX,
                                              dscale_accum);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;

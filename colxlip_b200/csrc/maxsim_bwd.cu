@@ -173,8 +173,8 @@ int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long l
   if (dtxt != nullptr) {
     const long long rows = static_cast<long long>(Bt) * T;
     dim3 grid(static_cast<unsigned>((rows + 7) / 8), (D + 32 * V - 1) / (32 * V));
-    if (dtype == CXL_DTYPE_BF16) maxsim_bwd_dtxt_kernel<__nv_bfloat16><<<grid, 256, 0, stream>>>(p);
-    else maxsim_bwd_dtxt_kernel<float><<<grid, 256, 0, stream>>>(p);
+    if (dtype == CXL_DTYPE_BF16) maxsim_bwd_dtxt_kernel<__nv_bfloat16><<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
+    else maxsim_bwd_dtxt_kernel<float><<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
     CXL_CUDA_CHECK(cudaGetLastError());
   }
   if (dimg != nullptr) {
@@ -187,11 +187,11 @@ int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long l
     if (dtype == CXL_DTYPE_BF16) {
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_bwd_dimg_kernel<__nv_bfloat16>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
-      maxsim_bwd_dimg_kernel<__nv_bfloat16><<<grid, DS, smem, stream>>>(p, DS);
+      maxsim_bwd_dimg_kernel<__nv_bfloat16><<<grid, DS, smem, CXL_COUNTED(stream)>>>(p, DS);
     } else {
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_bwd_dimg_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           static_cast<int>(smem)));
-      maxsim_bwd_dimg_kernel<float><<<grid, DS, smem, stream>>>(p, DS);
+      maxsim_bwd_dimg_kernel<float><<<grid, DS, smem, CXL_COUNTED(stream)>>>(p, DS);
     }
     CXL_CUDA_CHECK(cudaGetLastError());
   }

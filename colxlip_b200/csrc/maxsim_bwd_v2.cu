@@ -574,7 +574,7 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
   auto kern = maxsim_bwd_dtxt_v2_kernel<NWC, U16>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid((p.rows + ROWS - 1) / ROWS, p.D / DS);
-  kern<<<grid, (NWC + 1) * 32, smem_bytes, stream>>>(tm, p);
+  kern<<<grid, (NWC + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, p);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }
@@ -609,12 +609,12 @@ static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chun
     lp.k_first = p.k_off + k0;
     lp.n_img = n;
     const long long units = static_cast<long long>(n) * p.n_st;
-    lkern<<<static_cast<unsigned>((units + 7) / 8), 256, lists_smem, stream>>>(lp);
+    lkern<<<static_cast<unsigned>((units + 7) / 8), 256, lists_smem, CXL_COUNTED(stream)>>>(lp);
     CXL_CUDA_CHECK(cudaGetLastError());
     p.chunk_k0 = k0;
     p.chunk_n = n;
     dim3 grid(p.D / DS, (n + NIMG - 1) / NIMG);
-    kern<<<grid, (NW + 1) * 32, smem_bytes, stream>>>(tm, p);
+    kern<<<grid, (NW + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, p);
     CXL_CUDA_CHECK(cudaGetLastError());
   }
   return CXL_OK;
@@ -657,7 +657,7 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     p.hdr_words = round_up_i(nw * 4 * npo, 32);
     p.block_bytes = p.hdr_words * 4 + kStRows * 4;
     // scratch for the row lists of one chunk of images (stream-ordered allocation)
-    static const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4096);
+    static const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4608);
     const long long per_img = static_cast<long long>(p.n_st) * p.block_bytes;
     long long cap = (static_cast<long long>(scratch_mb) << 20) / per_img;
     if (cap >= Bi) {

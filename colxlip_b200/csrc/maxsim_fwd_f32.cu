@@ -156,7 +156,7 @@ int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, in
   CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
   if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs * sizeof(float), stream));
   dim3 grid(m_tiles, chunks);
-  maxsim_fwd_f32_kernel<<<grid, 256, 0, stream>>>(p);
+  maxsim_fwd_f32_kernel<<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
   CXL_CUDA_CHECK(cudaGetLastError());
   return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);
 }

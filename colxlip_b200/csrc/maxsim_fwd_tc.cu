@@ -551,7 +551,7 @@ int launch_maxsim_finalize(float* S, const float* cnt, size_t npairs, int T, int
   size_t fg = (npairs + fb - 1) / fb;
   if (fg > static_cast<size_t>(sms) * 16) fg = static_cast<size_t>(sms) * 16;
   if (fg == 0) return CXL_OK;
-  maxsim_finalize_kernel<<<static_cast<unsigned>(fg), fb, 0, stream>>>(S, cnt, npairs, 1.0f / static_cast<float>(T),
+  maxsim_finalize_kernel<<<static_cast<unsigned>(fg), fb, 0, CXL_COUNTED(stream)>>>(S, cnt, npairs, 1.0f / static_cast<float>(T),
                                                                       mean_mode);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
@@ -674,7 +674,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes;
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
       int ncl = q.num_units < clusters ? q.num_units : clusters;
-      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, stream>>>(tmA2, tmB2, q);
+      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
       CXL_CUDA_CHECK(cudaGetLastError());
       return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
     }
@@ -721,7 +721,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   int grid = p.num_units < sms ? p.num_units : sms;
   if (force_grid > 0 && force_grid < grid) grid = force_grid;
-  maxsim_fwd_tc_kernel<<<grid, kThreads, smem_bytes, stream>>>(tmA, tmB, p);
+  maxsim_fwd_tc_kernel<<<grid, kThreads, smem_bytes, CXL_COUNTED(stream)>>>(tmA, tmB, p);
   CXL_CUDA_CHECK(cudaGetLastError());
 
   return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);

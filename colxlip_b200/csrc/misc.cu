@@ -40,11 +40,11 @@ int pack_bf16(const void* src, int src_dtype, long long item_stride, long long r
   const size_t cap = static_cast<size_t>(num_sms()) * 32;
   if (blocks > cap) blocks = cap;
   if (src_dtype == CXL_DTYPE_F32)
-    pack_bf16_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+    pack_bf16_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, CXL_COUNTED(stream)>>>(
         reinterpret_cast<const float*>(src), item_stride, row_stride, items, n, n_pad, D,
         reinterpret_cast<__nv_bfloat16*>(dst));
   else if (src_dtype == CXL_DTYPE_BF16)
-    pack_bf16_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, stream>>>(
+    pack_bf16_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, CXL_COUNTED(stream)>>>(
         reinterpret_cast<const __nv_bfloat16*>(src), item_stride, row_stride, items, n, n_pad, D,
         reinterpret_cast<__nv_bfloat16*>(dst));
   else
@@ -72,7 +72,7 @@ int pair_weights(const float* dS, const float* cnt, const float* gscale, int mea
   size_t blocks = (static_cast<size_t>(n) + 255) / 256;
   const size_t cap = static_cast<size_t>(num_sms()) * 16;
   if (blocks > cap) blocks = cap;
-  pair_weights_kernel<<<static_cast<unsigned>(blocks), 256, 0, stream>>>(dS, cnt, gscale, mean_mode,
+  pair_weights_kernel<<<static_cast<unsigned>(blocks), 256, 0, CXL_COUNTED(stream)>>>(dS, cnt, gscale, mean_mode,
                                                                         1.0f / static_cast<float>(T),
                                                                         static_cast<size_t>(n), w);
   CXL_CUDA_CHECK(cudaGetLastError());
@@ -108,7 +108,7 @@ __global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __rest
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                    const int* target, int* rank_out, cudaStream_t stream) {
   if (rows <= 0 || cols <= 0) return CXL_ERR_INVALID_ARG;
-  rank_of_target_kernel<<<rows, 256, 0, stream>>>(scores, row_stride, col_stride, cols, target, rank_out);
+  rank_of_target_kernel<<<rows, 256, 0, CXL_COUNTED(stream)>>>(scores, row_stride, col_stride, cols, target, rank_out);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }

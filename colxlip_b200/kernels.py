@@ -43,10 +43,13 @@ class CudaKernels:
     """Thin wrappers; every method enqueues on the current CUDA stream of the tensors' device."""
 
     name = "cuda"
-    launches = 0  # number of our kernel-launching C-ABI calls (bench.py reports it)
 
     def __init__(self):
         self.lib = _lib.load()
+
+    def launches(self) -> int:
+        """CUDA kernels launched by the library in this process so far (bench.py reports the per-step delta)."""
+        return int(self.lib.cxl_kernel_launches())
 
     # ---- layout helpers ---------------------------------------------------------------------
     def img_row_stride(self, P: int, prec: str) -> int:
@@ -70,7 +73,6 @@ class CudaKernels:
             check(self.lib.cxl_pack_bf16(_ptr(x), CXL_DTYPE_F32 if x.dtype == torch.float32 else CXL_DTYPE_BF16,
                                          x.stride(0), x.stride(1), N, n, n_pad, D, _ptr(out), _stream()),
                   "cxl_pack_bf16")
-        CudaKernels.launches += 1
         return out
 
     def _alloc_argmax(self, Bt: int, Bi: int, T: int, P: int, dev) -> torch.Tensor:
@@ -97,7 +99,6 @@ class CudaKernels:
             check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D,
                                           CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
                                           _ptr(S), _ptr(cnt), _ptr(argmax), _stream()), "cxl_maxsim_fwd")
-        CudaKernels.launches += 2
         return S, cnt, argmax
 
     # ---- K2 --------------------------------------------------------------------------------------
@@ -109,7 +110,6 @@ class CudaKernels:
         with torch.cuda.device(dev):
             check(self.lib.cxl_pair_weights(_ptr(dS), _ptr(cnt), None, mean_mode, T, dS.numel(), _ptr(w), _stream()),
                   "cxl_pair_weights")
-        CudaKernels.launches += 1
         return w
 
     def maxsim_bwd(self, txt_op, img_op, argmax, w, T: int, P: int, prec: str,
@@ -129,7 +129,6 @@ class CudaKernels:
             check(fn(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img, T, P, D,
                      CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32,
                      ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
-        CudaKernels.launches += int(need_txt) + int(need_img)
         return dtxt, dimg
 
     # ---- K3 --------------------------------------------------------------------------------------
@@ -146,7 +145,6 @@ class CudaKernels:
             check(self.lib.cxl_infonce_stats(_ptr(X), _ptr(scale), B_loc, B, row0, _ptr(row_lse), _ptr(col_max),
                                              _ptr(col_sum), _ptr(diag), _ptr(ws), nbytes, _stream()),
                   "cxl_infonce_stats")
-        CudaKernels.launches += 3
         return row_lse, col_max, col_sum, diag
 
     def infonce_grad(self, X, scale, coef, row0: int, row_lse, col_lse, cnt=None, out=None):
@@ -159,7 +157,6 @@ class CudaKernels:
             check(self.lib.cxl_infonce_grad(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
                                             _ptr(col_lse), _ptr(cnt), _ptr(dX), _ptr(dscale), _stream()),
                   "cxl_infonce_grad")
-        CudaKernels.launches += 1
         return dX, dscale
 
     # ---- retrieval ---------------------------------------------------------------------------------
@@ -174,7 +171,6 @@ class CudaKernels:
         with torch.cuda.device(dev):
             check(self.lib.cxl_rank_of_target(_ptr(scores), scores.stride(0), scores.stride(1), R, C, _ptr(target),
                                               _ptr(out), _stream()), "cxl_rank_of_target")
-        CudaKernels.launches += 1
         return out
 
     # ---- debug / test hooks -------------------------------------------------------------------------

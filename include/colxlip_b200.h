@@ -39,6 +39,10 @@ extern "C" {
 #define CXL_MEAN_PLAIN 1  /* model.py:628   mean over all T tokens          */
 
 const char* cxl_strerror(int code);
+
+/* Number of CUDA kernels this library has launched in the process so far (all entry points; the dImg backward
+ * launches two kernels per chunk of images, so the count per call depends on the shape). */
+unsigned long long cxl_kernel_launches(void);
 const char* cxl_last_cuda_error(void);
 int cxl_version(void);
 /* 0 if the current device can run the kernels (compute capability 10.x), else CXL_ERR_NO_DEVICE. */
