@@ -36,6 +36,9 @@ WORKLOADS = {
     "small": (2048, 196, 77, 512, "reduced B=2048 P=196 T=77 D=512 (development only)"),
 }
 METRIC = "MaxSim-loss fwd+bwd image-text pairs/sec"
+# dram__bytes_read.sum + dram__bytes_write.sum of ONE K1 launch, from an ncu capture of the same launch shape
+# (not measurable live): (workload, n_gpus) -> (bytes, source file under profiles/)
+PROFILED_K1_TRAFFIC = {("cfg2", 1): (6771814875392 + 94268055040, "profiles/r2a_k1_cfg2_dram.csv")}
 
 
 def peaks():
@@ -267,7 +270,9 @@ def run_gpu(args):
     flops_rank = 2.0 * b * B * T * P * D
     ach = flops_rank / (k1 * 1e-3) / 1e12
     roofline = {"bound": "tensor", "kernel": "maxsim_fwd_tc2_kernel (K1, CTA-pair tcgen05)", "achieved": ach, "peak": pk["bf16_tflops"],
-                "unit": "TFLOP/s", "frac": ach / pk["bf16_tflops"], "traffic": None,
+                "unit": "TFLOP/s", "frac": ach / pk["bf16_tflops"],
+                "traffic": PROFILED_K1_TRAFFIC.get((args.workload, world), (None, None))[0],
+                "traffic_source": PROFILED_K1_TRAFFIC.get((args.workload, world), (None, None))[1],
                 "frac_of_sustained_peak": ach / pk["bf16_tflops_sustained"], "peak_source": pk["source"],
                 "kernel_ms": k1, "note": "K1 launch incl. its S/cnt memsets and the finalize kernel, timed alone"}
 

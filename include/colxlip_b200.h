@@ -97,7 +97,9 @@ int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev,
  * Image-shard calls (multi-GPU reduce-scatter pipeline): `img`/`dimg` point at the first of Bi
  * images of a shard, while w / argmax are the forward's full buffers over `ld_pairs` images and
  * the shard starts at image `k_off` of them (single call: ld_pairs = Bi, k_off = 0).
- * bf16 shapes with D % 128 == 0 and T >= 8 run the TMA-staged streaming kernels; the rest a generic kernel.
+ * bf16 shapes with D % 128 == 0, T >= 8 and P <= 576 run the TMA-staged kernels (dTxt gather; dImg = row-list
+ * pre-pass + gather, which takes up to CXL_DIMG_SCRATCH_MB (default 4608) MB of stream-ordered scratch from the
+ * device's default memory pool); the rest a generic kernel.
  */
 int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
                    int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
