@@ -50,24 +50,11 @@ struct __align__(8) V2Barriers {
 };
 
 
-__device__ __forceinline__ uint32_t pack_entry(float w, uint32_t lo16) {
-  return (static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(w))) << 16) | lo16;
+__device__ __forceinline__ uint32_t pack_entry_lo(float w, uint32_t hi16) {
+  return (hi16 << 16) | static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(w)));
 }
 
-// acc[0..7] += bf16x8(v) * bf16(high half of e)
-__device__ __forceinline__ void fhfma8(float (&a)[8], const uint4& v, uint32_t e) {
-  asm("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"
-      "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"
-      "mov.b32 {wl, wh}, %12;\n\t"
-      "fma.rn.f32.bf16 %0, x0, wh, %0;\n\t fma.rn.f32.bf16 %1, x1, wh, %1;\n\t"
-      "fma.rn.f32.bf16 %2, x2, wh, %2;\n\t fma.rn.f32.bf16 %3, x3, wh, %3;\n\t"
-      "fma.rn.f32.bf16 %4, x4, wh, %4;\n\t fma.rn.f32.bf16 %5, x5, wh, %5;\n\t"
-      "fma.rn.f32.bf16 %6, x6, wh, %6;\n\t fma.rn.f32.bf16 %7, x7, wh, %7;\n\t}"
-      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])
-      : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e));
-}
-
-// same, weight in the low half of e
+// acc[0..7] += bf16x8(v) * bf16(low half of e)
 __device__ __forceinline__ void fhfma8_lo(float (&a)[8], const uint4& v, uint32_t e) {
   asm("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"
       "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"
@@ -185,7 +172,8 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
 
   // entries of image 0
   mbar_wait(full0, 0);
-  sts32(ent_st, pack_entry(wr[0], ldq_smem(smem0 + q_off) * 8));   // slab row offset in 16-byte units (q*128/16)
+  // entry = slab row offset << 16 | bf16(w): bytes (q*128) when P <= 256, 16-byte units (q*8) otherwise
+  sts32(ent_st, pack_entry_lo(wr[0], ldq_smem(smem0 + q_off) * (U16 ? 8u : 128u)));
   __syncwarp();
 
   int stage = 0;                 // stage of image k
@@ -205,15 +193,15 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
         if (k + 1 < Bi) {
           mbar_wait(full0 + 8 * nstage, nphase);
           sts32(ent_st + ((b & 1) ^ 1) * 128,
-                pack_entry(wr[(b + 1) & 3], ldq_smem(smem0 + nstage * stage_bytes + q_off) * 8));
+                pack_entry_lo(wr[(b + 1) & 3], ldq_smem(smem0 + nstage * stage_bytes + q_off) * (U16 ? 8u : 128u)));
         }
         wr[b] = __ldg(wptr + min(k + 4, Bi - 1));
         const uint32_t stl = stl0 + stage * stage_bytes;
         const uint32_t e[8] = {ea.x, ea.y, ea.z, ea.w, eb.x, eb.y, eb.z, eb.w};
 #pragma unroll
         for (int jj = 0; jj < 8; ++jj) {
-          const uint4 v = lds128(stl + ((e[jj] & 0xFFFFu) << 4));
-          fhfma8(acc[jj], v, e[jj]);
+          const uint4 v = lds128(stl + (U16 ? ((e[jj] >> 16) << 4) : (e[jj] >> 16)));   // u8: one LEA.HI
+          fhfma8_lo(acc[jj], v, e[jj]);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * stage);
@@ -470,9 +458,11 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
         const int len = static_cast<int>(h[i][j] >> 16);
         uint32_t ep = ent + (h[i][j] & 0xFFFFu) * 4;
         const int maxlen = __reduce_max_sync(0xffffffffu, len);
+        // two items per trip, then at most one single; a quarter past the end of its own list takes a dummy
+        // entry (row 0 with weight +0)
+        int it = 0;
 #pragma unroll 1
-        for (int it = 0; it < maxlen; it += 2, ep += 8) {
-          // dummy entry past the end of this quarter's list: row 0 with weight +0
+        for (; it + 2 <= maxlen; it += 2, ep += 8) {
           uint32_t ea, eb;
           asm volatile("{\n\t.reg .pred pa, pb;\n\t"
                        "setp.lt.s32 pa, %3, %4;\n\t setp.lt.s32 pb, %5, %4;\n\t"
@@ -483,6 +473,14 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
           const uint4 vb = lds128(row_base + (eb >> 16));
           fhfma8_lo(acc[i][j], va, ea);
           fhfma8_lo(acc[i][j], vb, eb);
+        }
+        if (it < maxlen) {
+          uint32_t ea;
+          asm volatile("{\n\t.reg .pred pa;\n\t"
+                       "setp.lt.s32 pa, %2, %3;\n\t mov.b32 %0, 0;\n\t @pa ld.shared.b32 %0, [%1];\n\t}"
+                       : "=&r"(ea) : "r"(ep), "r"(it), "r"(len));
+          const uint4 va = lds128(row_base + (ea >> 16));
+          fhfma8_lo(acc[i][j], va, ea);
         }
       }
     }
