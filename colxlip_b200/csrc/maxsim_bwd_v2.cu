@@ -655,9 +655,9 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     p.hdr_words = round_up_i(nw * 4 * npo, 32);
     p.block_bytes = p.hdr_words * 4 + kStRows * 4;
     // scratch for the row lists of one chunk of images (stream-ordered allocation)
-    static const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4608);
+    const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4608);           // read per call: tests shrink it
     const long long per_img = static_cast<long long>(p.n_st) * p.block_bytes;
-    long long cap = (static_cast<long long>(scratch_mb) << 20) / per_img;
+    long long cap = (static_cast<long long>(scratch_mb < 1 ? 1 : scratch_mb) << 20) / per_img;
     if (cap >= Bi) {
       cap = Bi;
     } else {

@@ -171,6 +171,24 @@ def test_maxsim_backward_streaming_kernels(K, shape):
         assert torch.equal(torch.cat([d0, d1]), dimg)
 
 
+def test_dimg_is_deterministic_and_independent_of_the_chunking(K, monkeypatch):
+    """The dImg row lists are built per chunk of images (scratch budget CXL_DIMG_SCRATCH_MB); every image's lists
+    and accumulation order are fixed by the data alone, so any chunking -- and any rerun -- gives the same bits."""
+    Bt, Bi, T, P, D = 120, 23, 77, 196, 512          # 9240 rows = 19 super-tiles, ~56 KB of lists per image
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=41, pad_text=True, Bt=Bt)
+    txt_op = K.prepare(_rounded(tt).cuda(), T, "bf16")
+    img_op = K.prepare(_rounded(ti).cuda(), K.img_row_stride(P, "bf16"), "bf16")
+    S, cnt, arg = K.maxsim_fwd(txt_op, img_op, T, P, "bf16", O.MASKED, True)
+    w = K.pair_weights(torch.randn(Bt, Bi, generator=torch.Generator().manual_seed(6)).cuda(), cnt, T, O.MASKED)
+    _, base = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
+    _, again = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
+    assert torch.equal(base, again)
+    monkeypatch.setenv("CXL_DIMG_SCRATCH_MB", "1")   # 1 MB: chunks of a few images (odd tail chunk included)
+    _, chunked = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
+    torch.cuda.synchronize()
+    assert torch.equal(base, chunked)
+
+
 def test_all_zero_text_edge_case(K):
     """count = 0 + 1e-8: logit 0 and gradient factor 1e8 (SURVEY 7.2 edge semantics)."""
     from colxlip_b200 import loss as L
