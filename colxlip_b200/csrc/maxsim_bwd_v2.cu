@@ -13,11 +13,10 @@
 //   dTxt: CTA = (tile of 32*NWC text-token rows, 64-wide D slice).  The [P,64] slab of image k is staged once
 //         per CTA by TMA; a QUARTER warp handles one row (8 lanes x 8 channels = one 128 B slab row per
 //         LDS.128 phase, conflict-free), so one warp instruction serves four items.  Per-item entries
-//         (bf16 weight | slab row offset) are prepared by the consuming warp itself two images ahead.
-//   dImg: CTA = (image k, DS-wide D slice); consumer warp g owns patches [g*G, g*G+G) in registers.  Text-row
-//         tiles stream through a TMA ring (multicast to the C images of a cluster); producer warps bucket the
-//         tile's items into per-consumer queues (match.any ranks, no atomics), and the consumer dispatches on
-//         the patch with one brx.idx into straight-line FMA groups.
+//         (slab row offset | bf16 weight) are prepared by the consuming warp itself one image ahead.
+//   dImg: also a gather with static accumulators: a pre-pass sorts every 512-row super-tile of text rows by
+//         argmax patch (per image), then CTA = (2 images, 64-wide D slice) streams the super-tiles + the list
+//         blocks through a TMA ring and each quarter warp walks the row lists of the patches it owns.
 #include "common.cuh"
 
 namespace cxl {
@@ -46,7 +45,6 @@ struct BwdV2Params {
 struct __align__(8) V2Barriers {
   uint64_t full[8];
   uint64_t empty[8];
-  uint64_t ready[8];    // cluster leader only: every CTA of the cluster has freed + armed the stage
 };
 
 
@@ -677,8 +675,18 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
       CXL_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
       pool_set[dev] = true;
     }
+    // when the device is nearly full (the framework's own allocator holds the rest) settle for smaller chunks
     void* scratch = nullptr;
-    CXL_CUDA_CHECK(cudaMallocAsync(&scratch, static_cast<size_t>(cap * per_img), stream));
+    for (;;) {
+      const cudaError_t ae = cudaMallocAsync(&scratch, static_cast<size_t>(cap * per_img), stream);
+      if (ae == cudaSuccess) break;
+      (void)cudaGetLastError();
+      if (ae != cudaErrorMemoryAllocation || cap <= nimg) {
+        set_cuda_error(ae, "cudaMallocAsync (dImg lists)");
+        return CXL_ERR_CUDA;
+      }
+      cap = (cap / 2 + nimg - 1) / nimg * nimg;
+    }
     p.lists = static_cast<const uint8_t*>(scratch);
     if (npo == 2) rc = launch_dimg_v3<25, 2, 2>(txt, p, max_smem, static_cast<int>(cap), stream);
     else if (npo == 3) rc = launch_dimg_v3<25, 3, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
