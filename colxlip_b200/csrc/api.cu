@@ -36,7 +36,8 @@ int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, in
                    float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi,
                int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-               int accumulate_img, int force_generic, cudaStream_t stream);
+               int accumulate_img, int force_generic, void* ws, size_t ws_bytes, cudaStream_t stream);
+size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D);
 int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
                  cudaStream_t stream);
 size_t infonce_workspace_bytes(int B_loc, int B);
@@ -128,7 +129,7 @@ int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev,
 
 static int bwd_entry(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
                      int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
-                     int force_generic, void* stream) {
+                     int force_generic, void* ws, size_t ws_bytes, void* stream) {
   if (txt == nullptr || img == nullptr || argmax == nullptr || w == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
   if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
@@ -136,13 +137,26 @@ static int bwd_entry(const void* txt, const void* img, const void* argmax, const
   if (rc != CXL_OK) return rc;
   const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
   return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
-                    dimg, accumulate_img, force_generic, static_cast<cudaStream_t>(stream));
+                    dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
                    int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
                    void* stream) {
-  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 0, stream);
+  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 0, nullptr,
+                   0, stream);
+}
+
+size_t cxl_maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D, int dtype) {
+  if (dtype != CXL_DTYPE_BF16 || Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return 0;
+  return maxsim_bwd_workspace_bytes(Bt, Bi, T, P, D);
+}
+
+int cxl_maxsim_bwd_ws(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                      int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
+                      void* ws, size_t ws_bytes, void* stream) {
+  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 0, ws,
+                   ws_bytes, stream);
 }
 
 size_t cxl_infonce_workspace_bytes(int B_loc, int B) { return infonce_workspace_bytes(B_loc, B); }
@@ -208,7 +222,7 @@ int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T
 int cxl_maxsim_bwd_generic(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
                            int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg,
                            int accumulate_img, void* stream) {
-  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 1, stream);
+  return bwd_entry(txt, img, argmax, w, Bt, Bi, T, P, D, dtype, ld_pairs, k_off, dtxt, dimg, accumulate_img, 1, nullptr, 0, stream);
 }
 
 }  // extern "C"

@@ -621,13 +621,61 @@ static int env_int(const char* name, int dflt) {
   return (s != nullptr && *s != 0) ? atoi(s) : dflt;
 }
 
-// returns CXL_ERR_UNSUPPORTED when the shape is outside the fast path (caller falls back to the generic kernels)
+static bool stream_path_covers(const void* txt, const void* img, int Bt, int T, int P, int D) {
+  if (D % 128 != 0 || P > 576 || T < 8) return false;
+  if (static_cast<long long>(Bt) * T >= (1LL << 31)) return false;
+  if ((reinterpret_cast<uintptr_t>(txt) & 15) || (reinterpret_cast<uintptr_t>(img) & 15)) return false;
+  return true;
+}
+
+// dImg plan: kernel variant (consumer warps x patches per quarter warp x images per CTA), list-block geometry and
+// how many images' row lists fit `budget_bytes` of scratch (whole waves of the gather kernel when chunking)
+struct DimgPlan {
+  int npo, nw, nimg, n_st, hdr_words, block_bytes;
+  long long per_img;   // scratch bytes per image
+  long long cap;       // images per chunk
+};
+static DimgPlan dimg_plan(int Bt, int Bi, int T, int P, long long budget_bytes) {
+  DimgPlan d;
+  d.npo = P <= 200 ? 2 : P <= 300 ? 3 : 8;
+  d.nw = P <= 300 ? 25 : 19;
+  d.nimg = P <= 200 ? 2 : 1;
+  d.n_st = (Bt * T + kStRows - 1) / kStRows;
+  d.hdr_words = round_up_i(d.nw * 4 * d.npo, 32);
+  d.block_bytes = d.hdr_words * 4 + kStRows * 4;
+  d.per_img = static_cast<long long>(d.n_st) * d.block_bytes;
+  long long cap = budget_bytes / d.per_img;
+  if (cap >= Bi) {
+    cap = Bi;
+  } else {
+    const long long per_wave = static_cast<long long>(num_sms()) * d.nimg;   // images per D/64 waves (1 CTA/SM)
+    if (cap >= per_wave) cap = cap / per_wave * per_wave;
+    cap = cap / d.nimg * d.nimg;
+  }
+  d.cap = cap;
+  return d;
+}
+static long long dimg_budget_bytes() {
+  const int mb = env_int("CXL_DIMG_SCRATCH_MB", 4608);       // read per call: tests shrink it
+  return static_cast<long long>(mb < 1 ? 1 : mb) << 20;
+}
+
+// preferred workspace of maxsim_bwd_stream for this shape (0: none needed / shape not on the fast path)
+size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D) {
+  if (D % 128 != 0 || P > 576 || T < 8 || static_cast<long long>(Bt) * T >= (1LL << 31)) return 0;
+  DimgPlan d = dimg_plan(Bt, Bi, T, P, dimg_budget_bytes());
+  if (d.cap < d.nimg) d.cap = d.nimg;
+  return static_cast<size_t>(d.cap * d.per_img);
+}
+
+// returns CXL_ERR_UNSUPPORTED when the shape is outside the fast path (caller falls back to the generic kernels).
+// ws/ws_bytes: caller-provided scratch for the dImg row lists (16-byte aligned; see maxsim_bwd_workspace_bytes);
+// ws == nullptr: stream-ordered allocation from the device's default memory pool.
 int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt,
                       int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-                      int accumulate_img, cudaStream_t stream) {
-  if (D % 128 != 0 || P > 576 || T < 8) return CXL_ERR_UNSUPPORTED;
-  if (static_cast<long long>(Bt) * T >= (1LL << 31)) return CXL_ERR_UNSUPPORTED;
-  if ((reinterpret_cast<uintptr_t>(txt) & 15) || (reinterpret_cast<uintptr_t>(img) & 15)) return CXL_ERR_UNSUPPORTED;
+                      int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream) {
+  if (!stream_path_covers(txt, img, Bt, T, P, D)) return CXL_ERR_UNSUPPORTED;
+  if (ws != nullptr && (reinterpret_cast<uintptr_t>(ws) & 15)) return CXL_ERR_INVALID_ARG;
   BwdV2Params p;
   memset(&p, 0, sizeof(p));
   p.w = w; p.argmax = argmax; p.ld_arg = ld_arg;
@@ -645,56 +693,46 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     if (rc != CXL_OK) return rc;
   }
   if (dimg != nullptr) {
-    // variant: consumer warps x patches per quarter warp x images per CTA
-    const int npo = P <= 200 ? 2 : P <= 300 ? 3 : 8;
-    const int nw = P <= 300 ? 25 : 19;
-    const int nimg = P <= 200 ? 2 : 1;
-    p.n_st = (p.rows + kStRows - 1) / kStRows;
-    p.hdr_words = round_up_i(nw * 4 * npo, 32);
-    p.block_bytes = p.hdr_words * 4 + kStRows * 4;
-    // scratch for the row lists of one chunk of images (stream-ordered allocation)
-    const int scratch_mb = env_int("CXL_DIMG_SCRATCH_MB", 4608);           // read per call: tests shrink it
-    const long long per_img = static_cast<long long>(p.n_st) * p.block_bytes;
-    long long cap = (static_cast<long long>(scratch_mb < 1 ? 1 : scratch_mb) << 20) / per_img;
-    if (cap >= Bi) {
-      cap = Bi;
+    DimgPlan d = dimg_plan(Bt, Bi, T, P, ws != nullptr ? static_cast<long long>(ws_bytes) : dimg_budget_bytes());
+    p.n_st = d.n_st;
+    p.hdr_words = d.hdr_words;
+    p.block_bytes = d.block_bytes;
+    long long cap = d.cap;
+    void* scratch = ws;
+    if (ws != nullptr) {
+      if (cap < d.nimg && cap < Bi) return CXL_ERR_WORKSPACE;
     } else {
-      // whole waves: the gather kernel runs D/64 CTAs per image group, one CTA per SM
-      int sms = 148;
-      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-      const long long per_wave = static_cast<long long>(sms) * nimg;           // images per (D/64) waves
-      if (cap >= per_wave) cap = cap / per_wave * per_wave;
-      cap = cap / nimg * nimg;
-      if (cap < nimg) cap = nimg;
-    }
-    static bool pool_set[64] = {false};
-    if (dev < 64 && !pool_set[dev]) {           // keep freed scratch cached in the device's pool between calls
-      cudaMemPool_t pool;
-      CXL_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
-      unsigned long long keep = ~0ull;
-      CXL_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
-      pool_set[dev] = true;
-    }
-    // when the device is nearly full (the framework's own allocator holds the rest) settle for smaller chunks
-    void* scratch = nullptr;
-    for (;;) {
-      const cudaError_t ae = cudaMallocAsync(&scratch, static_cast<size_t>(cap * per_img), stream);
-      if (ae == cudaSuccess) break;
-      (void)cudaGetLastError();
-      if (ae != cudaErrorMemoryAllocation || cap <= nimg) {
-        set_cuda_error(ae, "cudaMallocAsync (dImg lists)");
-        return CXL_ERR_CUDA;
+      if (cap < d.nimg) cap = d.nimg;
+      static bool pool_set[64] = {false};
+      if (dev < 64 && !pool_set[dev]) {           // keep freed scratch cached in the device's pool between calls
+        cudaMemPool_t pool;
+        CXL_CUDA_CHECK(cudaDeviceGetDefaultMemPool(&pool, dev));
+        unsigned long long keep = ~0ull;
+        CXL_CUDA_CHECK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+        pool_set[dev] = true;
       }
-      cap = (cap / 2 + nimg - 1) / nimg * nimg;
+      // when the device is nearly full (the framework's own allocator holds the rest) settle for smaller chunks
+      for (;;) {
+        const cudaError_t ae = cudaMallocAsync(&scratch, static_cast<size_t>(cap * d.per_img), stream);
+        if (ae == cudaSuccess) break;
+        (void)cudaGetLastError();
+        if (ae != cudaErrorMemoryAllocation || cap <= d.nimg) {
+          set_cuda_error(ae, "cudaMallocAsync (dImg lists)");
+          return CXL_ERR_CUDA;
+        }
+        cap = (cap / 2 + d.nimg - 1) / d.nimg * d.nimg;
+      }
     }
     p.lists = static_cast<const uint8_t*>(scratch);
-    if (npo == 2) rc = launch_dimg_v3<25, 2, 2>(txt, p, max_smem, static_cast<int>(cap), stream);
-    else if (npo == 3) rc = launch_dimg_v3<25, 3, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
+    if (d.npo == 2) rc = launch_dimg_v3<25, 2, 2>(txt, p, max_smem, static_cast<int>(cap), stream);
+    else if (d.npo == 3) rc = launch_dimg_v3<25, 3, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
     else rc = launch_dimg_v3<19, 8, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
-    const cudaError_t fe = cudaFreeAsync(scratch, stream);
-    if (rc == CXL_OK && fe != cudaSuccess) {
-      set_cuda_error(fe, "cudaFreeAsync (dImg lists)");
-      rc = CXL_ERR_CUDA;
+    if (ws == nullptr) {
+      const cudaError_t fe = cudaFreeAsync(scratch, stream);
+      if (rc == CXL_OK && fe != cudaSuccess) {
+        set_cuda_error(fe, "cudaFreeAsync (dImg lists)");
+        rc = CXL_ERR_CUDA;
+      }
     }
     if (rc != CXL_OK) return rc;
   }

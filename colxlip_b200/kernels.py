@@ -114,7 +114,7 @@ class CudaKernels:
 
     def maxsim_bwd(self, txt_op, img_op, argmax, w, T: int, P: int, prec: str,
                    need_txt: bool = True, need_img: bool = True, k_off: int = 0, n_img: Optional[int] = None,
-                   generic: bool = False):
+                   generic: bool = False, library_scratch: bool = False):
         """w: [Bt, ld_pairs] fp32 pair weights (pair_weights / infonce_grad with cnt)."""
         dev = _require_cuda(txt_op, img_op, argmax, w)
         Bt, D = txt_op.shape[0], txt_op.shape[2]
@@ -124,11 +124,23 @@ class CudaKernels:
         dtxt = torch.empty((Bt, T, D), dtype=torch.float32, device=dev) if need_txt else None
         dimg = torch.empty((n_img, P, D), dtype=torch.float32, device=dev) if need_img else None
         img_shard = img_op[k_off:k_off + n_img]
+        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
         with torch.cuda.device(dev):
-            fn = self.lib.cxl_maxsim_bwd_generic if generic else self.lib.cxl_maxsim_bwd
-            check(fn(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img, T, P, D,
-                     CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32,
-                     ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
+            if generic:
+                check(self.lib.cxl_maxsim_bwd_generic(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img,
+                                                      T, P, D, dt, ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()),
+                      "cxl_maxsim_bwd_generic")
+            elif library_scratch:
+                # plain entry point: the library takes the dImg scratch from the device's default CUDA memory pool
+                check(self.lib.cxl_maxsim_bwd(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img, T, P, D,
+                                              dt, ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _stream()), "cxl_maxsim_bwd")
+            else:
+                # scratch for the dImg row lists comes from torch's caching allocator (no second memory pool)
+                nws = int(self.lib.cxl_maxsim_bwd_workspace_bytes(Bt, n_img, T, P, D, dt)) if need_img else 0
+                ws = torch.empty(nws, dtype=torch.uint8, device=dev) if nws > 0 else None
+                check(self.lib.cxl_maxsim_bwd_ws(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img, T, P,
+                                                 D, dt, ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _ptr(ws), nws, _stream()),
+                      "cxl_maxsim_bwd_ws")
         return dtxt, dimg
 
     # ---- K3 --------------------------------------------------------------------------------------

@@ -105,6 +105,16 @@ int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const f
                    int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
                    void* stream);
 
+/* Same, with caller-provided scratch for the dImg row lists (no allocation inside the library).
+ * cxl_maxsim_bwd_workspace_bytes() is the preferred size for a call with these dimensions (0 when the shape
+ * needs none); a smaller `ws` makes the library work through the images in smaller chunks, CXL_ERR_WORKSPACE
+ * if not even one CTA's images fit.  `ws` must be 16-byte aligned and is only used until the call's kernels
+ * finish on `stream`.  cxl_maxsim_bwd() itself takes the same scratch from the device's default memory pool. */
+size_t cxl_maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D, int dtype);
+int cxl_maxsim_bwd_ws(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                      int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
+                      void* ws, size_t ws_bytes, void* stream);
+
 /*
  * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,
  * columns = all B images; labels are the diagonal).  Replaces `logit_scale *` and the

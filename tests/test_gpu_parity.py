@@ -183,10 +183,13 @@ def test_dimg_is_deterministic_and_independent_of_the_chunking(K, monkeypatch):
     _, base = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
     _, again = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
     assert torch.equal(base, again)
+    _, pooled = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, library_scratch=True)
+    assert torch.equal(base, pooled)                 # cxl_maxsim_bwd (library-side scratch) == cxl_maxsim_bwd_ws
     monkeypatch.setenv("CXL_DIMG_SCRATCH_MB", "1")   # 1 MB: chunks of a few images (odd tail chunk included)
     _, chunked = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
+    _, chunked_pool = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, library_scratch=True)
     torch.cuda.synchronize()
-    assert torch.equal(base, chunked)
+    assert torch.equal(base, chunked) and torch.equal(base, chunked_pool)
 
 
 def test_all_zero_text_edge_case(K):
