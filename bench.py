@@ -232,12 +232,17 @@ def run_gpu(args):
     from colxlip_b200.kernels import default_kernels
     l0 = default_kernels().launches()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    marks = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps - 1)]
     e0.record()
-    for _ in range(args.steps):
+    for i in range(args.steps):
         loss = step(feats)
+        if i < args.steps - 1:
+            marks[i].record()                       # per-step split times (this rank; the headline is e0..e1)
     e1.record()
     barrier()
     clocks = sampler.stop()
+    edges = [e0] + marks + [e1]
+    step_ms_each = [edges[i].elapsed_time(edges[i + 1]) for i in range(args.steps)]
     launches = default_kernels().launches() - l0     # our kernels inside the timed region (this rank)
     ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
     if world > 1:
@@ -316,7 +321,11 @@ def run_gpu(args):
                        "input_dtype": args.input_dtype, "autocast": "bf16", "alpha": 0.5, "logit_scale": 1 / 0.07,
                        "l2": "inputs (GBs) far larger than the 126 MB L2; no flush needed",
                        "step_frac_of_bf16_peak": step_flops / (ms_per_step * 1e-3) / world / (pk["bf16_tflops"] * 1e12),
-                       "loss": loss_val},
+                       "step_frac_of_sustained_bf16_peak":
+                           step_flops / (ms_per_step * 1e-3) / world / (pk["bf16_tflops_sustained"] * 1e12),
+                       "interactions_per_s": float(B) * B / (ms_per_step * 1e-3),
+                       "step_ms_each_rank0": step_ms_each, "step_ms_median": sorted(step_ms_each)[len(step_ms_each) // 2],
+                       "step_ms_best": min(step_ms_each), "loss": loss_val},
             "roofline": roofline,
             "e2e": {"value": B / (e2e_ms * 1e-3), "unit": "pairs/s", "h2d_bytes_per_step": h2d_bytes,
                     "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": n_e2e},
