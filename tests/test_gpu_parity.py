@@ -185,6 +185,11 @@ def test_dimg_is_deterministic_and_independent_of_the_chunking(K, monkeypatch):
     assert torch.equal(base, again)
     _, pooled = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, library_scratch=True)
     assert torch.equal(base, pooled)                 # cxl_maxsim_bwd (library-side scratch) == cxl_maxsim_bwd_ws
+    # dTxt runs one launch per block of images (L2 residency) and accumulates in place: 8 + 8 + 7 images here
+    dt_one, _ = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_img=False)
+    monkeypatch.setenv("CXL_DTXT_BLOCK_MB", "0")
+    dt_blk, _ = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_img=False)
+    assert torch.equal(dt_one, dt_blk)               # same order of additions per output element
     monkeypatch.setenv("CXL_DIMG_SCRATCH_MB", "1")   # 1 MB: chunks of a few images (odd tail chunk included)
     _, chunked = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False)
     _, chunked_pool = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_txt=False, library_scratch=True)
