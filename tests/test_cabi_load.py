@@ -38,6 +38,33 @@ def test_pure_functions_and_error_strings():
     assert lib.cxl_img_row_stride(196) == 196 and lib.cxl_img_row_stride(49) == 56 and lib.cxl_img_row_stride(1) == 8
     assert b"no CPU fallback" in lib.cxl_strerror(-4)
     assert lib.cxl_strerror(0) == b"ok"
+    assert b"workspace" in lib.cxl_strerror(-5)
+    assert lib.cxl_kernel_launches() >= 0            # process-wide launch counter (0 until a kernel runs)
+
+
+def test_backward_workspace_sizing(monkeypatch):
+    """cxl_maxsim_bwd_workspace_bytes: scratch for the dImg row lists = images-per-chunk x super-tiles x block."""
+    from colxlip_b200 import _lib
+    lib = _lib.load()
+    BF16, F32 = 1, 0
+    # cfg-2 geometry: 2523136 rows -> 4928 super-tiles of 512 rows; block = 224 header words + 512 entries
+    per_img = 4928 * (224 * 4 + 512 * 4)
+    n = lib.cxl_maxsim_bwd_workspace_bytes(32768, 32768, 77, 196, 512, BF16)
+    assert n % per_img == 0 and n <= 4608 << 20
+    imgs = n // per_img
+    assert imgs % (2 * 148) == 0 and imgs >= 296     # whole waves of the gather kernel (2 images per CTA, 148 SMs)
+    # everything fits: one chunk
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 77, 196, 512, BF16) == 10 * 10 * (224 * 4 + 2048)
+    # shapes served by the generic kernels need none
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 77, 196, 512, F32) == 0
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 77, 196, 96, BF16) == 0
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 4, 196, 512, BF16) == 0
+    # P > 200 / P > 300 variants: wider headers (300 -> 320 words, 19*4*8 = 608 words)
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 3, 77, 300, 128, BF16) == 3 * 10 * (320 * 4 + 2048)
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 3, 77, 576, 128, BF16) == 3 * 10 * (608 * 4 + 2048)
+    monkeypatch.setenv("CXL_DIMG_SCRATCH_MB", "1")
+    small = lib.cxl_maxsim_bwd_workspace_bytes(120, 23, 77, 196, 512, BF16)
+    assert small <= 1 << 20 and small % (19 * (224 * 4 + 2048)) == 0 and small // (19 * 2944) == 18
 
 
 @pytest.mark.skipif(torch.cuda.is_available(), reason="checks the no-GPU failure mode")
