@@ -306,24 +306,40 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgLi
     if (U16) adst[1] = make_uint4(a[4], a[5], a[6], a[7]);
     int m = static_cast<int>(g0 / p.T);
     int rem = static_cast<int>(g0 - static_cast<long long>(m) * p.T);
-    float wv = (g0 < p.rows) ? __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol) : 0.f;
     uint32_t wpk[8];
+    if (p.T >= 16 && nrows == kStRows) {
+      // common case (full super-tile, a lane's 16 rows span at most two texts): straight-line
+      const int nb = p.T - rem;                            // rows of this lane that still belong to text m
+      const float w0 = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
+      const float w1 = (nb < 16) ? __ldg(p.w + static_cast<size_t>(m + 1) * p.ld_pairs + kcol) : 0.f;
+      const uint32_t b0 = __bfloat16_as_ushort(__float2bfloat16_rn(w0));
+      const uint32_t b1 = __bfloat16_as_ushort(__float2bfloat16_rn(w1));
 #pragma unroll
-    for (int i = 0; i < 16; ++i) {
-      uint32_t wb = 0u;
-      if (rl + i < nrows) {
-        if (rem == p.T) {
-          rem = 0;
-          ++m;
-          wv = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
-        }
-        ++rem;
+      for (int i = 0; i < 16; i += 2) wpk[i >> 1] = (i < nb ? b0 : b1) | ((i + 1 < nb ? b0 : b1) << 16);
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
         const uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
         atomicAdd(&cur[min(q, q_max)], 1u);
-        wb = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
       }
-      if (i & 1) wpk[i >> 1] |= wb << 16;
-      else wpk[i >> 1] = wb;
+    } else {
+      float wv = (g0 < p.rows) ? __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol) : 0.f;
+#pragma unroll
+      for (int i = 0; i < 16; ++i) {
+        uint32_t wb = 0u;
+        if (rl + i < nrows) {
+          if (rem == p.T) {
+            rem = 0;
+            ++m;
+            wv = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
+          }
+          ++rem;
+          const uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
+          atomicAdd(&cur[min(q, q_max)], 1u);
+          wb = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
+        }
+        if (i & 1) wpk[i >> 1] |= wb << 16;
+        else wpk[i >> 1] = wb;
+      }
     }
     uint4* wdst = reinterpret_cast<uint4*>(wrow) + lane * 2;
     wdst[0] = make_uint4(wpk[0], wpk[1], wpk[2], wpk[3]);
