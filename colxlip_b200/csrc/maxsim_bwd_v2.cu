@@ -374,15 +374,13 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgLi
     const bool valid = r < nrows;
     const uint32_t q = min(static_cast<uint32_t>(U16 ? arg16[r] : arg8[r]), q_max);
     const uint32_t mask = __match_any_sync(0xffffffffu, valid ? q : 0xFFFFFFFFu);
+    const uint32_t base = valid ? cur[q] : 0u;           // every lane of a group reads the cursor ...
+    __syncwarp();
     const uint32_t rank = __popc(mask & lt_mask);
-    const int leader = __ffs(mask) - 1;
-    uint32_t base = 0;
-    if (valid && rank == 0) {
-      base = cur[q];
-      cur[q] = base + __popc(mask);
+    if (valid) {
+      if (rank == 0) cur[q] = base + __popc(mask);       // ... before its first lane moves it on
+      ent[base + rank] = (static_cast<uint32_t>(r * 128) << 16) | static_cast<uint32_t>(wrow[r]);
     }
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (valid) ent[base + rank] = (static_cast<uint32_t>(r * 128) << 16) | static_cast<uint32_t>(wrow[r]);
     __syncwarp();
   }
   uint4* dst = reinterpret_cast<uint4*>(p.lists + static_cast<size_t>(unit) * p.block_bytes);
