@@ -105,7 +105,8 @@ int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const f
                    int D, int dtype, int ld_pairs, int k_off, float* dtxt, float* dimg, int accumulate_img,
                    void* stream);
 
-/* Same, with caller-provided scratch for the dImg row lists (no allocation inside the library).
+/* Same computation (autograd of loss.py:34-44), with caller-provided scratch for the dImg row lists (no
+ * allocation inside the library): this is the entry the Python mirror binds.
  * cxl_maxsim_bwd_workspace_bytes() is the preferred size for a call with these dimensions (0 when the shape
  * needs none); a smaller `ws` makes the library work through the images in smaller chunks, CXL_ERR_WORKSPACE
  * if not even one CTA's images fit.  `ws` must be 16-byte aligned and is only used until the call's kernels
