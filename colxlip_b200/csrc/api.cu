@@ -34,9 +34,10 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
                   cudaStream_t stream);
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
                    float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
-int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi,
-               int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-               int accumulate_img, int force_generic, void* ws, size_t ws_bytes, cudaStream_t stream);
+int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
+               const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
+               float* dtxt, float* dimg, int accumulate_img, int force_generic, void* ws, size_t ws_bytes,
+               cudaStream_t stream);
 size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D);
 int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
                  cudaStream_t stream);
@@ -136,8 +137,24 @@ static int bwd_entry(const void* txt, const void* img, const void* argmax, const
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
-  return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
-                    dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+  return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), 0, w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off,
+                    dtxt, dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
+                             int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
+                             int force_generic, void* stream) {
+  if (img == nullptr || argmax == nullptr || w == nullptr || dtxt == nullptr) return CXL_ERR_INVALID_ARG;
+  if (Bt_total <= 0 || m0 < 0 || m_cnt <= 0 || m0 + m_cnt > Bt_total) return CXL_ERR_INVALID_ARG;
+  if (Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  // dTxt never reads the text operand; `img` stands in for the (unused) txt pointer of the shared dispatcher
+  return maxsim_bwd(img, img, argmax, cxl_argmax_ld(Bt_total, T), static_cast<long long>(m0) * T,
+                    w + static_cast<size_t>(m0) * ld_pairs, m_cnt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
+                    nullptr, 0, force_generic, nullptr, 0, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
@@ -163,7 +180,7 @@ size_t cxl_infonce_workspace_bytes(int B_loc, int B) { return infonce_workspace_
 
 int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse,
                       float* col_max, float* col_sum, float* diag, void* ws, size_t ws_bytes, void* stream) {
-  if (!X || !scale_dev || !row_lse || !col_max || !col_sum || !diag || !ws) return CXL_ERR_INVALID_ARG;
+  if (!X || !scale_dev || !row_lse || !diag) return CXL_ERR_INVALID_ARG;   // col_max/col_sum/ws: all null = rows only
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   return infonce_stats(X, scale_dev, B_loc, B, row0, row_lse, col_max, col_sum, diag, ws, ws_bytes,
@@ -173,7 +190,7 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                      const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
                      void* stream) {
-  if (!X || !scale_dev || !coef_dev || !row_lse || !col_lse || !dX || !dscale_accum) return CXL_ERR_INVALID_ARG;
+  if (!X || !scale_dev || !coef_dev || !row_lse || !dX || !dscale_accum) return CXL_ERR_INVALID_ARG;  // col_lse may be null
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX, dscale_accum,

@@ -100,6 +100,7 @@ __global__ void infonce_col_combine_kernel(const float* __restrict__ pmax, const
 }
 
 // ---- gradient: dX = coef*scale*(softmax_row + softmax_col - 2*delta); dscale += sum(coef*(...)*X) ----
+// (rows-only when col_lse is null: dX = coef*scale*(softmax_row - delta))
 __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const float* __restrict__ scale_p,
                                                            const float* __restrict__ coef_p, int B_loc, int B, int row0,
                                                            const float* __restrict__ row_lse,
@@ -118,8 +119,10 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
   for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B; c += gridDim.x * blockDim.x) {
     const float xv = x[c];
     const float sx = scale * xv;
-    float t = expf(sx - rl) + expf(sx - col_lse[c]);
-    if (c == diag_c) t -= 2.f;
+    // col_lse == nullptr: rows-only cross-entropy (ClipLoss local_loss, loss.py:144-146): softmax_row - delta
+    float t = expf(sx - rl);
+    if (col_lse) t += expf(sx - col_lse[c]);
+    if (c == diag_c) t -= col_lse ? 2.f : 1.f;
     t *= coef;
     ds = fmaf(t, xv, ds);
     const float dxv = t * scale;
@@ -145,12 +148,14 @@ size_t infonce_workspace_bytes(int B_loc, int B) {
 int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse, float* col_max,
                   float* col_sum, float* diag, void* ws, size_t ws_bytes, cudaStream_t stream) {
   if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
-  if (ws_bytes < infonce_workspace_bytes(B_loc, B)) return CXL_ERR_WORKSPACE;
+  if ((col_max == nullptr) != (col_sum == nullptr)) return CXL_ERR_INVALID_ARG;
+  if (col_max != nullptr && (ws == nullptr || ws_bytes < infonce_workspace_bytes(B_loc, B))) return CXL_ERR_WORKSPACE;
   const int nblk = (B_loc + kColRowsPerBlock - 1) / kColRowsPerBlock;
   float* pmax = reinterpret_cast<float*>(ws);
   float* psum = pmax + static_cast<size_t>(nblk) * B;
   infonce_row_kernel<<<B_loc, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B, row0, row_lse, diag);
   CXL_CUDA_CHECK(cudaGetLastError());
+  if (col_max == nullptr && col_sum == nullptr) return CXL_OK;   // rows-only statistics (ClipLoss local_loss)
   dim3 g((B + 511) / 512, nblk);
   infonce_col_partial_kernel<<<g, 128, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B_loc, B, pmax, psum);
   CXL_CUDA_CHECK(cudaGetLastError());

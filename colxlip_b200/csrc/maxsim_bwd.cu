@@ -146,25 +146,30 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
   }
 }
 
-int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt,
-                      int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-                      int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream);
+int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
+                      const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
+                      float* dtxt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream);
 
-int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi,
-               int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-               int accumulate_img, int force_generic, void* ws, size_t ws_bytes, cudaStream_t stream) {
+// arg_row_off != 0: txt / w / dtxt point at a slice of Bt texts whose first flat text-token row is `arg_row_off`
+// inside the forward's argmax rows (pitch ld_arg); only dTxt can be computed from a row slice.
+int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
+               const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
+               float* dtxt, float* dimg, int accumulate_img, int force_generic, void* ws, size_t ws_bytes,
+               cudaStream_t stream) {
   if (ld_pairs < Bi + k_off || k_off < 0) return CXL_ERR_INVALID_ARG;
-  if (ld_arg < static_cast<long long>(Bt) * T) return CXL_ERR_INVALID_ARG;
+  if (arg_row_off < 0 || ld_arg < arg_row_off + static_cast<long long>(Bt) * T) return CXL_ERR_INVALID_ARG;
+  if (arg_row_off != 0 && dimg != nullptr) return CXL_ERR_INVALID_ARG;
   if (dtype == CXL_DTYPE_BF16 && !force_generic) {
     // fast path: TMA-staged streaming kernels; shapes it does not cover fall through to the generic kernels
-    const int rc = maxsim_bwd_stream(txt, img, argmax, ld_arg, w, Bt, Bi, T, P, D, p_stride, ld_pairs, k_off, dtxt,
-                                     dimg, accumulate_img, ws, ws_bytes, stream);
+    const int rc = maxsim_bwd_stream(txt, img, argmax, ld_arg, arg_row_off, w, Bt, Bi, T, P, D, p_stride, ld_pairs,
+                                     k_off, dtxt, dimg, accumulate_img, ws, ws_bytes, stream);
     if (rc != CXL_ERR_UNSUPPORTED) return rc;
   }
   const int V = dtype == CXL_DTYPE_BF16 ? 8 : 4;
   if (D % V != 0) return CXL_ERR_UNSUPPORTED;
   BwdParams p;
-  p.txt = txt; p.img = img; p.argmax = argmax; p.ld_arg = ld_arg; p.w = w;
+  p.txt = txt; p.img = img; p.ld_arg = ld_arg; p.w = w;
+  p.argmax = static_cast<const uint8_t*>(argmax) + arg_row_off * (P > 256 ? 2 : 1);
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D; p.p_stride = p_stride;
   p.ld_pairs = ld_pairs; p.k_off = k_off;
   p.argmax_u16 = P > 256;

@@ -23,8 +23,9 @@ namespace cxl {
 
 struct BwdV2Params {
   const float* w;       // [Bt, ld_pairs]  per-pair weight dL/dS / cnt
-  const void* argmax;   // [k_off + Bi][ld_arg]  image-major
+  const void* argmax;   // [k_off + Bi][ld_arg]  image-major (already advanced to this call's first text row)
   long long ld_arg;
+  long long arg_avail;  // elements of an argmax row from this call's first text row to the end of the pitch
   int Bt, Bi, T, P, D, p_stride;
   int rows;             // Bt*T
   int ld_pairs, k_off, argmax_u16;
@@ -118,7 +119,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
   if (warp == NWC) {
     if (lane == 0) {
       // argmax elements of this CTA's rows (clamped to the padded row length; both multiples of 16 bytes)
-      const long long avail = p.ld_arg - r0;
+      const long long avail = p.arg_avail - r0;
       const uint32_t qbytes = static_cast<uint32_t>((avail < ROWS ? avail : ROWS) * ES);
       const uint8_t* qsrc = reinterpret_cast<const uint8_t*>(p.argmax) +
                             (static_cast<size_t>(p.k_off) * p.ld_arg + r0) * ES;
@@ -715,14 +716,18 @@ size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D) {
 // returns CXL_ERR_UNSUPPORTED when the shape is outside the fast path (caller falls back to the generic kernels).
 // ws/ws_bytes: caller-provided scratch for the dImg row lists (16-byte aligned; see maxsim_bwd_workspace_bytes);
 // ws == nullptr: stream-ordered allocation from the device's default memory pool.
-int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, const float* w, int Bt,
-                      int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off, float* dtxt, float* dimg,
-                      int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream) {
+// arg_row_off: first text-token row of this call inside the argmax rows (row-slice calls, dTxt only).
+int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
+                      const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
+                      float* dtxt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream) {
   if (!stream_path_covers(txt, img, Bt, T, P, D)) return CXL_ERR_UNSUPPORTED;
+  const int es = P > 256 ? 2 : 1;
+  if ((arg_row_off * es) % 16 != 0) return CXL_ERR_UNSUPPORTED;     // bulk copies of argmax runs need 16 B alignment
+  argmax = static_cast<const uint8_t*>(argmax) + arg_row_off * es;
   if (ws != nullptr && (reinterpret_cast<uintptr_t>(ws) & 15)) return CXL_ERR_INVALID_ARG;
   BwdV2Params p;
   memset(&p, 0, sizeof(p));
-  p.w = w; p.argmax = argmax; p.ld_arg = ld_arg;
+  p.w = w; p.argmax = argmax; p.ld_arg = ld_arg; p.arg_avail = ld_arg - arg_row_off;
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D; p.p_stride = p_stride;
   p.rows = Bt * T;
   p.ld_pairs = ld_pairs; p.k_off = k_off; p.argmax_u16 = P > 256;

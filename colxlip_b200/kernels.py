@@ -143,12 +143,33 @@ class CudaKernels:
                       "cxl_maxsim_bwd_ws")
         return dtxt, dimg
 
+    def maxsim_bwd_dtxt_rows(self, img_op, argmax, w, Bt_total: int, m0: int, m_cnt: int, T: int, P: int, prec: str,
+                             generic: bool = False):
+        """dTxt [m_cnt,T,D] of texts m0..m0+m_cnt-1 only (all images); argmax / w are the forward's full buffers.
+        The sub-batch backward of the gradient-accumulation loop (reference train.py:166-183)."""
+        dev = _require_cuda(img_op, argmax, w)
+        D = img_op.shape[2]
+        assert w.is_contiguous() and w.dtype == torch.float32 and w.shape[0] == Bt_total
+        dtxt = torch.empty((m_cnt, T, D), dtype=torch.float32, device=dev)
+        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_maxsim_bwd_dtxt_rows(_ptr(img_op), _ptr(argmax), _ptr(w), Bt_total, m0, m_cnt,
+                                                    img_op.shape[0], T, P, D, dt, w.shape[1], 0, _ptr(dtxt),
+                                                    1 if generic else 0, _stream()), "cxl_maxsim_bwd_dtxt_rows")
+        return dtxt
+
     # ---- K3 --------------------------------------------------------------------------------------
-    def infonce_stats(self, X: torch.Tensor, scale: torch.Tensor, row0: int):
+    def infonce_stats(self, X: torch.Tensor, scale: torch.Tensor, row0: int, rows_only: bool = False):
+        """rows_only: just (row_lse, None, None, diag) -- the one-directional CE of ClipLoss(local_loss=True)."""
         dev = _require_cuda(X, scale)
         B_loc, B = X.shape
         row_lse = torch.empty(B_loc, dtype=torch.float32, device=dev)
         diag = torch.empty(B_loc, dtype=torch.float32, device=dev)
+        if rows_only:
+            with torch.cuda.device(dev):
+                check(self.lib.cxl_infonce_stats(_ptr(X), _ptr(scale), B_loc, B, row0, _ptr(row_lse), None, None,
+                                                 _ptr(diag), None, 0, _stream()), "cxl_infonce_stats")
+            return row_lse, None, None, diag
         col_max = torch.empty(B, dtype=torch.float32, device=dev)
         col_sum = torch.empty(B, dtype=torch.float32, device=dev)
         nbytes = int(self.lib.cxl_infonce_workspace_bytes(B_loc, B))
@@ -160,7 +181,8 @@ class CudaKernels:
         return row_lse, col_max, col_sum, diag
 
     def infonce_grad(self, X, scale, coef, row0: int, row_lse, col_lse, cnt=None, out=None):
-        """dX (or, with cnt, the MaxSim pair weights dX / (cnt + 1e-8)); `out` may alias X."""
+        """dX (or, with cnt, the MaxSim pair weights dX / (cnt + 1e-8)); `out` may alias X.
+        col_lse=None: rows-only gradient coef/(2B) * scale * (softmax_row - delta)."""
         dev = _require_cuda(X, scale, coef, row_lse, col_lse)
         B_loc, B = X.shape
         dX = torch.empty_like(X) if out is None else out

@@ -258,16 +258,32 @@ class _ColClipLossFn(torch.autograd.Function):
             dist.all_reduce(dscale, group=group)
 
         need = ctx.needs_input_grad
-        # K2: token gradients from the saved argmax
-        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
-                                              need_txt=need[3], need_img=need[2])
         d_txt = dG @ g_img if need[1] else None
         d_img_all = dG.T @ g_txt if need[0] else None
-
-        # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
-        # reproduces the reference's x world_size (every rank back-propagates the same full loss).
         mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
-        dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
+        rows = cfg.get("grad_rows")
+        if rows is None:
+            # K2: token gradients from the saved argmax
+            dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
+                                                  need_txt=need[3], need_img=need[2])
+            # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
+            # reproduces the reference's x world_size (every rank back-propagates the same full loss).
+            dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
+        else:
+            # gradient-accumulation call (train.py:166-183): only samples lo..hi-1 of every rank's batch carry
+            # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items; the rest stays zero
+            lo, hi = rows
+            n = hi - lo
+            dtxt_tok = dimg_tok = None
+            if need[3]:
+                dtxt_tok = torch.zeros((b, T, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
+                dtxt_tok[lo:hi] = k.maxsim_bwd_dtxt_rows(img_op, argmax, w, b, lo, n, T, P, prec)
+            if need[2]:
+                parts = [k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
+                                      k_off=r * b + lo, n_img=n)[1] for r in range(W)]
+                home = _reduce_scatter_rows(torch.cat(parts) if W > 1 else parts[0], W, group)
+                dimg_tok = torch.zeros((b, P, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
+                dimg_tok[lo:hi] = home
         d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
 
         def fin(x, dt):
@@ -379,6 +395,17 @@ class ColClipLoss(nn.Module):
             "alpha": self.alpha, "gather_with_grad": self.gather_with_grad,
             "prec": _select_precision(token_image_features, token_text_features),
         }
+        # Extension for the reference's gradient-accumulation loop (train.py:166-183): grad_rows=(lo, hi) declares
+        # that only samples lo..hi-1 of this rank's batch carry gradient (the live sub-batch inside the cat of cached
+        # features).  Token-feature gradients outside the slice are returned as zeros -- torch.cat's backward drops
+        # them anyway -- and K2 does 1/accum_freq of the work.  The reference's forward swallows unknown kwargs, so
+        # the same call is valid against it.
+        rows = kwargs.get("grad_rows")
+        if rows is not None:
+            lo, hi = int(rows[0]), int(rows[1])
+            if not (0 <= lo < hi <= token_text_features.shape[0]):
+                raise ValueError("grad_rows must satisfy 0 <= lo < hi <= local batch")
+            cfg["grad_rows"] = (lo, hi)
         losses = _ColClipLossFn.apply(image_features, text_features, token_image_features, token_text_features,
                                       logit_scale, cfg)
         global_contrastive_loss, token_contrastive_loss, total_loss = losses[0], losses[1], losses[2]
@@ -386,3 +413,178 @@ class ColClipLoss(nn.Module):
             return {"global_contrastive_loss": global_contrastive_loss,
                     "token_contrastive_loss": token_contrastive_loss, "total_loss": total_loss}
         return total_loss
+
+
+# ---------------------------------------------------------------------------------------------------
+# ClipLoss (reference loss.py:95-182): the global-embedding InfoNCE alone, for the non-colxlip models the
+# reference's factory also serves.  Same K3 kernels; the [b,B] logit block is a library GEMM.
+# ---------------------------------------------------------------------------------------------------
+def _select_global_precision(*tensors: torch.Tensor) -> str:
+    mode = _PRECISION
+    if mode == "auto":
+        autocast = torch.is_autocast_enabled("cuda") if tensors[0].is_cuda else False
+        low = all(t.dtype in (torch.bfloat16, torch.float16) for t in tensors)
+        mode = "bf16" if (autocast or low) else "fp32"
+    return mode
+
+
+class _ClipLossFn(torch.autograd.Function):
+    """total_loss of ClipLoss.forward.  Two layouts:
+    symmetric (local_loss=False, or one rank): this rank's text rows against ALL images, row + column CE;
+    local     (local_loss=True, W > 1): the reference's two one-directional [b,B] blocks (loss.py:144-146)."""
+
+    @staticmethod
+    def forward(ctx, image_features, text_features, logit_scale, cfg):
+        with torch.autocast(image_features.device.type, enabled=False):
+            return _ClipLossFn._forward(ctx, image_features, text_features, logit_scale, cfg)
+
+    @staticmethod
+    def _forward(ctx, image_features, text_features, logit_scale, cfg):
+        k = cfg["kernels"]
+        W, rank, group, prec = cfg["world_size"], cfg["rank"], cfg.get("group"), cfg["prec"]
+        b = image_features.shape[0]
+        B, row0 = b * W, rank * b
+        dev = image_features.device
+        local = bool(cfg["local_loss"]) and W > 1
+        a_img = _round_like_gemm_input(image_features, prec)
+        a_txt = _round_like_gemm_input(text_features, prec)
+        all_img = _all_gather_cat(a_img, W, group)
+        scale = logit_scale.detach().float().reshape(1).to(dev)
+        if not local:
+            G = a_txt @ all_img.T                                     # rows = this rank's texts
+            row_lse, col_max, col_sum, diag = k.infonce_stats(G, scale, row0)
+            col_lse = col_max + torch.log(col_sum)
+            part = row_lse.sum() - 2.0 * diag.sum()
+            if W > 1:
+                col_lse = torch.logsumexp(_all_gather_cat(col_lse.unsqueeze(0), W, group), dim=0)
+                dist.all_reduce(part, group=group)
+            loss = (part + col_lse.sum()) / (2.0 * B)
+            ctx.save_for_backward(G, a_txt, all_img, scale, row_lse, col_lse)
+        else:
+            all_txt = _all_gather_cat(a_txt, W, group)
+            X_i = a_img @ all_txt.T                                   # logits_per_image of this rank's images
+            X_t = a_txt @ all_img.T                                   # logits_per_text of this rank's texts
+            rl_i, _, _, dg_i = k.infonce_stats(X_i, scale, row0, rows_only=True)
+            rl_t, _, _, dg_t = k.infonce_stats(X_t, scale, row0, rows_only=True)
+            loss = ((rl_i - dg_i).sum() + (rl_t - dg_t).sum()) / (2.0 * b)
+            ctx.save_for_backward(X_i, X_t, a_img, a_txt, all_img, all_txt, scale, rl_i, rl_t)
+        ctx.cfg, ctx.local = cfg, local
+        ctx.meta = (b, B, row0, image_features.dtype, text_features.dtype, logit_scale.dtype, logit_scale.shape)
+        return loss
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        cfg = ctx.cfg
+        k = cfg["kernels"]
+        W, group = cfg["world_size"], cfg.get("group")
+        gwg = bool(cfg["gather_with_grad"]) and W > 1
+        b, B, row0, dt_img, dt_txt, dt_ls, ls_shape = ctx.meta
+        need = ctx.needs_input_grad
+        g = g.float().reshape(1).contiguous()
+        if not ctx.local:
+            G, a_txt, all_img, scale, row_lse, col_lse = ctx.saved_tensors
+            dG, dscale = k.infonce_grad(G, scale, g, row0, row_lse, col_lse)
+            if W > 1:
+                dist.all_reduce(dscale, group=group)              # every rank holds the full-batch loss
+            d_txt = dG @ all_img if need[1] else None
+            d_img = _reduce_scatter_rows(dG.T @ a_txt, W, group) if need[0] else None
+            mult = float(W) if gwg else 1.0                       # autograd all_gather sums W identical losses
+            if mult != 1.0:
+                d_txt = d_txt * mult if d_txt is not None else None
+                d_img = d_img * mult if d_img is not None else None
+        else:
+            X_i, X_t, a_img, a_txt, all_img, all_txt, scale, rl_i, rl_t = ctx.saved_tensors
+            coef = g * (float(B) / float(b))                      # the kernel divides by 2B; the loss by 2b
+            dX_i, ds_i = k.infonce_grad(X_i, scale, coef, row0, rl_i, None)
+            dX_t, ds_t = k.infonce_grad(X_t, scale, coef, row0, rl_t, None)
+            dscale = ds_i + ds_t                                  # this rank's own loss: no reduction
+            d_img = dX_i @ all_txt if need[0] else None
+            d_txt = dX_t @ all_img if need[1] else None
+            if gwg:                                               # gathered operands carry grad home (SUM)
+                if need[1]:
+                    d_txt = d_txt + _reduce_scatter_rows(dX_i.T @ a_img, W, group)
+                if need[0]:
+                    d_img = d_img + _reduce_scatter_rows(dX_t.T @ a_txt, W, group)
+        d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[2] else None
+        return (d_img.to(dt_img) if d_img is not None else None,
+                d_txt.to(dt_txt) if d_txt is not None else None, d_ls, None)
+
+
+class ClipLoss(nn.Module):
+    """Symmetric InfoNCE over global image/text embeddings (reference loss.py:95-182), same constructor and call
+    signatures; `forward` is one autograd node over the K3 kernels with logit rows sharded over ranks."""
+
+    def __init__(
+            self,
+            local_loss=False,
+            gather_with_grad=False,
+            cache_labels=False,
+            rank=0,
+            world_size=1,
+            use_horovod=False,
+            **kwargs
+    ):
+        super().__init__()
+        self.local_loss = local_loss
+        self.gather_with_grad = gather_with_grad
+        self.cache_labels = cache_labels
+        self.rank = rank
+        self.world_size = world_size
+        self.use_horovod = use_horovod
+        self.prev_num_logits = 0
+        self.labels = {}
+        self._kernels = kwargs.get("kernels", None)
+        self._group = kwargs.get("group", None)
+
+    _k = ColClipLoss._k
+    get_ground_truth = ColClipLoss.get_ground_truth
+
+    def get_logits(self, image_features, text_features, logit_scale, logit_bias=None):
+        """(logits_per_image, logits_per_text), materialised with torch ops as in the reference (loss.py:132-160)."""
+        if self.world_size > 1:
+            all_image_features, all_text_features = gather_features(
+                image_features, text_features, local_loss=self.local_loss, gather_with_grad=self.gather_with_grad,
+                rank=self.rank, world_size=self.world_size, use_horovod=self.use_horovod)
+            if self.local_loss:
+                logits_per_image = logit_scale * image_features @ all_text_features.T
+                logits_per_text = logit_scale * text_features @ all_image_features.T
+            else:
+                logits_per_image = logit_scale * all_image_features @ all_text_features.T
+                logits_per_text = logits_per_image.T
+        else:
+            logits_per_image = logit_scale * image_features @ text_features.T
+            logits_per_text = logit_scale * text_features @ image_features.T
+        if logit_bias is not None:
+            if self.world_size > 1 and not self.local_loss:
+                # in-place add through the transposed view as well (loss.py:157-158): 2 x bias on both
+                logits_per_image = logits_per_image + 2 * logit_bias
+                logits_per_text = logits_per_image.T
+            else:
+                logits_per_image = logits_per_image + logit_bias
+                logits_per_text = logits_per_text + logit_bias
+        return logits_per_image, logits_per_text
+
+    def forward(
+            self,
+            image_features=None,
+            text_features=None,
+            logit_scale=None,
+            logit_bias=None,
+            output_dict=False,
+            logits_per_image=None,
+            logits_per_text=None,
+            **kwargs,
+    ):
+        # logit_bias / logits_per_* are accepted and ignored exactly as in the reference (loss.py:172)
+        if self.world_size > 1 and self.use_horovod:
+            raise RuntimeError("horovod is not supported by colxlip_b200")
+        if image_features.dim() != 2 or text_features.dim() != 2 or image_features.shape != text_features.shape:
+            raise ValueError("ClipLoss expects image_features and text_features of the same [B, D] shape")
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        cfg = {"kernels": self._k(), "world_size": self.world_size, "rank": self.rank, "group": self._group,
+               "gather_with_grad": self.gather_with_grad, "local_loss": self.local_loss,
+               "prec": _select_global_precision(image_features, text_features)}
+        total_loss = _ClipLossFn.apply(image_features, text_features, logit_scale, cfg)
+        return {"total_loss": total_loss} if output_dict else total_loss

@@ -44,3 +44,92 @@ def compute_retrieval(similarity_scores, txt2img: Sequence[int], img2txt: Sequen
     t2i_np = t2i_ranks.cpu().numpy().astype(np.float64)
     i2t_np = best.cpu().numpy().astype(np.float64)
     return {**_report(t2i_np, "text_to_image"), **_report(i2t_np, "image_to_text")}
+
+
+# ---------------------------------------------------------------------------------------------------
+# MaxSim retrieval loop.  The reference's retrieval_on_split (train.py:510-585) is a leftover
+# of its FLAIR ancestry: it scores global embeddings only and calls model methods ColXLIP does not define.
+# The functions below keep its call shape (loaders + index dicts -> metrics dict with the same keys) and
+# score with the model's own token-level scorer (model.py:611-629) on the K1 kernel.
+# ---------------------------------------------------------------------------------------------------
+def _mean_scores(token_image_features, token_text_features, kernels=None):
+    from .loss import _maxsim
+    from .kernels import MEAN
+    return _maxsim(token_image_features, token_text_features, MEAN, kernels)
+
+
+def maxsim_score_matrix(token_image_features, token_text_features, image_chunk: int = 8192, text_chunk: int = 8192,
+                        kernels=None):
+    """i2t score matrix [N_img, N_txt] = compute_colbert_similarity(...).T (model.py:626-628), built block by
+    block so that neither operand copy nor the [chunk, chunk] score block grows with the gallery."""
+    n_img, n_txt = token_image_features.shape[0], token_text_features.shape[0]
+    out = torch.empty((n_img, n_txt), dtype=torch.float32, device=token_image_features.device)
+    with torch.no_grad():
+        for t0 in range(0, n_txt, text_chunk):
+            txt = token_text_features[t0:t0 + text_chunk]
+            for i0 in range(0, n_img, image_chunk):
+                s = _mean_scores(token_image_features[i0:i0 + image_chunk], txt, kernels)   # [txt, img]
+                out[i0:i0 + image_chunk, t0:t0 + text_chunk] = s.t()
+    return out
+
+
+def _unwrap_model(model):
+    return model.module if hasattr(model, "module") else model            # train.py:61-65
+
+
+def remap_indices(merged_img_ids, cap_ids, img2txt_dict, txt2img_dict):
+    """Gallery order -> positions (train.py:430-454): image ids are renumbered by their position in the
+    image loader's output; caption ids are expected to be 0..N-1 already."""
+    mapping = {int(old): new for new, old in enumerate(merged_img_ids)}
+    new_img2txt = {mapping[i]: list(caps) for i, caps in img2txt_dict.items()}
+    new_txt2img = {c: mapping[txt2img_dict[c][0]] for c in txt2img_dict.keys()}
+    return new_img2txt, new_txt2img
+
+
+def compute_similarity_scores_maxsim(model, img_loader, all_text_token_features, device, input_dtype, autocast,
+                                     kernels=None):
+    """Token-level counterpart of compute_similarity_scores_original_clip (train.py:587-614): stream the image
+    loader, score every image batch against ALL text tokens, return (scores [M, N] on `device`, img_ids)."""
+    blocks, all_img_ids = [], []
+    m = _unwrap_model(model)
+    for images, img_id in img_loader:
+        images = images.to(device=device, dtype=input_dtype, non_blocking=True)
+        all_img_ids.append(img_id.detach().cpu())
+        with autocast():
+            _, image_tokens = m.encode_image(images, normalize=True)
+            logit_scale = m.logit_scale.exp()
+            s = _mean_scores(image_tokens, all_text_token_features, kernels)                         # [N, b]
+        blocks.append((logit_scale.float() * s.t()).detach())
+    return torch.cat(blocks), torch.cat(all_img_ids)
+
+
+def retrieval_on_split(keyword, model, txt_loader, img_loader, img2txt_dict, txt2img_dict, args, epoch, metrics,
+                       device, input_dtype, autocast, kernels=None):
+    """Same signature and metric keys as the reference (train.py:510-585); text tokens stay on the device."""
+    num_txt_samples = txt_loader.num_samples
+    num_img_samples = img_loader.num_samples
+    m = _unwrap_model(model)
+    text_tokens, cap_ids = [], []
+    with torch.no_grad():
+        for texts, cap_id in txt_loader:
+            texts = texts.to(device=device, non_blocking=True)
+            with autocast():
+                _, tok = m.encode_text(texts, normalize=True)
+            text_tokens.append(tok.detach())
+            cap_ids.append(cap_id.detach().cpu())
+        all_text_tokens = torch.cat(text_tokens)
+        cap_ids = torch.cat(cap_ids)
+        scores, img_ids = compute_similarity_scores_maxsim(m, img_loader, all_text_tokens, device, input_dtype,
+                                                           autocast, kernels)
+        new_img2txt, new_txt2img = remap_indices(img_ids, cap_ids, img2txt_dict, txt2img_dict)
+        n_txt = scores.shape[1]
+        retrieval_metrics = compute_retrieval(scores, [new_txt2img[c] for c in range(n_txt)],
+                                              [new_img2txt[i] for i in range(scores.shape[0])], kernels=kernels)
+    if keyword != '':
+        keyword = keyword + '_'
+        retrieval_metrics = {keyword + k: v for k, v in retrieval_metrics.items()}
+    if "epoch" not in metrics:
+        metrics.update({"epoch": epoch})
+    metrics.update({**retrieval_metrics, f"{keyword}num_text_samples": num_txt_samples,
+                    f"{keyword}num_image_samples": num_img_samples})
+    return metrics

@@ -117,10 +117,25 @@ int cxl_maxsim_bwd_ws(const void* txt, const void* img, const void* argmax, cons
                       void* ws, size_t ws_bytes, void* stream);
 
 /*
+ * dTxt of a SLICE of the texts: rows m0 .. m0+m_cnt-1 of the forward's Bt_total texts, against images
+ * k_off .. k_off+Bi-1.  `argmax` and `w` are the forward's full buffers (pitches cxl_argmax_ld(Bt_total,T) and
+ * ld_pairs), `img` points at image k_off, dtxt [m_cnt,T,D] f32 is overwritten.  Serves the reference's
+ * gradient-accumulation loop (train.py:166-183), where only one sub-batch of the concatenated features
+ * carries gradient: together with an image-shard call of cxl_maxsim_bwd_ws (dimg only, k_off = the sub-batch)
+ * the backward does 1/accum_freq of the full work.  The TMA-staged kernel needs m0*T*elem_bytes % 16 == 0;
+ * other offsets run the generic kernel.
+ */
+int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
+                             int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
+                             int force_generic, void* stream);
+
+/*
  * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,
  * columns = all B images; labels are the diagonal).  Replaces `logit_scale *` and the
  * F.cross_entropy pairs of loss.py:252-263, 285-293.
  * Stats pass: row log-sum-exp [B_loc] and per-rank column (max, sumexp) partials [2,B] of scale*X.
+ * col_max, col_sum and ws may all be NULL: only the row statistics are computed (the one-directional CEs of
+ * ClipLoss with local_loss=True, loss.py:144-146).
  */
 size_t cxl_infonce_workspace_bytes(int B_loc, int B);
 int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0,
@@ -130,10 +145,13 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
  * Gradient pass: dX[m,k] = coef * scale * (exp(scale*X - row_lse[m]) + exp(scale*X - col_lse[k]) - 2*delta)
  * with coef = *coef_dev / (2B); dscale_partial += sum(dX/scale * X) (one float, atomically added).
  * If cnt != NULL (token logits) the output is the MaxSim pair weight dX / (cnt + 1e-8) instead of dX.
+ * If col_lse == NULL only the row cross-entropy is differentiated: dX = coef * scale * (exp(scale*X - row_lse[m]) - delta)
+ * -- the two one-directional CEs of ClipLoss with local_loss=True (loss.py:144-146,173-176); the caller folds
+ * its own normalisation into *coef_dev (the kernel still divides by 2B).
  * dX may alias X.
  */
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
-                     const float* row_lse, const float* col_lse /*[B] global*/, const float* cnt /*[B_loc,B] or NULL*/,
+                     const float* row_lse, const float* col_lse /*[B] global, or NULL*/, const float* cnt /*[B_loc,B] or NULL*/,
                      float* dX, float* dscale_accum, void* stream);
 
 /*

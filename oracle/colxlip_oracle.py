@@ -20,6 +20,8 @@ Reference lines followed (all relative to /root/reference/src/colxlip/):
   ColClipLossOracle.get_logits           loss.py:223-269
   ColClipLossOracle.forward              loss.py:271-296
   compute_retrieval                      train.py:457-508
+  clip_loss / clip_loss_local            loss.py:95-182   (ClipLoss; the multi-rank cases are pinned by
+                                                           tests/golden/dist_w2.npz = the reference under 2 gloo ranks)
 """
 from __future__ import annotations
 
@@ -139,6 +141,32 @@ class ColClipLossOracle:
         if output_dict:
             return {"global_contrastive_loss": g, "token_contrastive_loss": t, "total_loss": total}
         return total
+
+
+def clip_loss(image_features, text_features, logit_scale) -> torch.Tensor:
+    """ClipLoss.forward on one process / on the gathered global batch (loss.py:147-148 or 150-151, 172-181)."""
+    logits_per_image = logit_scale * image_features @ text_features.T
+    logits_per_text = logit_scale * text_features @ image_features.T
+    labels = torch.arange(logits_per_image.shape[0], device=logits_per_image.device)
+    return (F.cross_entropy(logits_per_image, labels) + F.cross_entropy(logits_per_text, labels)) / 2
+
+
+def clip_loss_local(image_features, text_features, logit_scale, rank: int, world_size: int,
+                    all_image_features=None, all_text_features=None) -> torch.Tensor:
+    """ClipLoss with local_loss=True as rank `rank` of `world_size` sees it (loss.py:144-146, 118-119): its own
+    b images against all texts and its own b texts against all images, labels offset by b*rank.  The
+    gathered operands default to the inputs themselves (single-process emulation: slices of the same leaf,
+    which reproduces gather_with_grad=True when the per-rank losses are summed); pass detached copies for
+    gather_with_grad=False."""
+    B = image_features.shape[0]
+    b = B // world_size
+    sl = slice(rank * b, (rank + 1) * b)
+    all_img = image_features if all_image_features is None else all_image_features
+    all_txt = text_features if all_text_features is None else all_text_features
+    logits_per_image = logit_scale * image_features[sl] @ all_txt.T
+    logits_per_text = logit_scale * text_features[sl] @ all_img.T
+    labels = torch.arange(b, device=image_features.device) + b * rank
+    return (F.cross_entropy(logits_per_image, labels) + F.cross_entropy(logits_per_text, labels)) / 2
 
 
 def loss_and_grads(image_features, text_features, token_image_features, token_text_features,

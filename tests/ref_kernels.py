@@ -56,9 +56,19 @@ class TorchRefKernels:
                 dimg[k].index_add_(0, arg[:, k].reshape(-1), contrib)
         return dtxt, dimg
 
-    def infonce_stats(self, X, scale, row0):
+    def maxsim_bwd_dtxt_rows(self, img_op, argmax, w, Bt_total, m0, m_cnt, T, P, prec, generic=False):
+        D = img_op.shape[2]
+        dtxt = torch.zeros(m_cnt, T, D)
+        for k in range(img_op.shape[0]):
+            dtxt += w[m0:m0 + m_cnt, k, None, None] * img_op[k][argmax[m0:m0 + m_cnt, k]]
+        return dtxt
+
+    def infonce_stats(self, X, scale, row0, rows_only=False):
         Z = X * scale
         row_lse = torch.logsumexp(Z, dim=1)
+        if rows_only:
+            idx = torch.arange(X.shape[0])
+            return row_lse, None, None, Z[idx, row0 + idx]
         col_max = Z.max(dim=0).values
         col_sum = torch.exp(Z - col_max).sum(dim=0)
         idx = torch.arange(X.shape[0])
@@ -68,9 +78,11 @@ class TorchRefKernels:
     def infonce_grad(self, X, scale, coef, row0, row_lse, col_lse, cnt=None, out=None):
         B_loc, B = X.shape
         Z = X * scale
-        t = torch.exp(Z - row_lse[:, None]) + torch.exp(Z - col_lse[None, :])
+        t = torch.exp(Z - row_lse[:, None])
+        if col_lse is not None:
+            t = t + torch.exp(Z - col_lse[None, :])
         idx = torch.arange(B_loc)
-        t[idx, row0 + idx] -= 2.0
+        t[idx, row0 + idx] -= 2.0 if col_lse is not None else 1.0
         t = t * (coef / (2.0 * B))
         dX = t * scale
         if cnt is not None:
