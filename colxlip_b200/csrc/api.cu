@@ -52,6 +52,11 @@ int pack_bf16(const void* src, int src_dtype, long long item_stride, long long r
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                    const int* target, int* rank_out, cudaStream_t stream);
 
+int l2norm_fwd(const void* x, int x_dtype, long long rows, int D, void* y, int y_dtype, float* inv_norm,
+               cudaStream_t stream);
+int l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const float* inv_norm, long long rows, int D,
+               void* dx, int dx_dtype, cudaStream_t stream);
+
 static int device_ok() {
   int dev = 0, major = 0;
   if (cudaGetDevice(&dev) != cudaSuccess) return CXL_ERR_NO_DEVICE;
@@ -195,6 +200,22 @@ int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_d
   if (rc != CXL_OK) return rc;
   return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX, dscale_accum,
                       static_cast<cudaStream_t>(stream));
+}
+
+int cxl_l2norm_fwd(const void* x, int x_dtype, long long rows, int D, void* y, int y_dtype, float* inv_norm,
+                   void* stream) {
+  if (!x || !y) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return l2norm_fwd(x, x_dtype, rows, D, y, y_dtype, inv_norm, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const float* inv_norm, long long rows,
+                   int D, void* dx, int dx_dtype, void* stream) {
+  if (!y || !g || !inv_norm || !dx) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return l2norm_bwd(y, y_dtype, g, g_dtype, inv_norm, rows, D, dx, dx_dtype, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,

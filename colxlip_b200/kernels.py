@@ -193,6 +193,37 @@ class CudaKernels:
                   "cxl_infonce_grad")
         return dX, dscale
 
+    # ---- producer side: L2 normalise + operand cast -----------------------------------
+    @staticmethod
+    def _dt(t: torch.Tensor) -> int:
+        if t.dtype == torch.float32:
+            return CXL_DTYPE_F32
+        if t.dtype == torch.bfloat16:
+            return CXL_DTYPE_BF16
+        raise RuntimeError(f"colxlip_b200: unsupported dtype {t.dtype} (float32 / bfloat16 only)")
+
+    def l2norm_fwd(self, x: torch.Tensor, out_dtype: torch.dtype, save_inv: bool = True):
+        """x [..., D] (f32|bf16, contiguous) -> (y [..., D] out_dtype, inv_norm [rows] f32 or None)."""
+        dev = _require_cuda(x)
+        D = x.shape[-1]
+        rows = x.numel() // D
+        y = torch.empty(x.shape, dtype=out_dtype, device=dev)
+        inv = torch.empty(rows, dtype=torch.float32, device=dev) if save_inv else None
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_l2norm_fwd(_ptr(x), self._dt(x), rows, D, _ptr(y), self._dt(y), _ptr(inv), _stream()),
+                  "cxl_l2norm_fwd")
+        return y, inv
+
+    def l2norm_bwd(self, y: torch.Tensor, g: torch.Tensor, inv: torch.Tensor, out_dtype: torch.dtype):
+        dev = _require_cuda(y, g, inv)
+        D = y.shape[-1]
+        rows = y.numel() // D
+        dx = torch.empty(y.shape, dtype=out_dtype, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_l2norm_bwd(_ptr(y), self._dt(y), _ptr(g), self._dt(g), _ptr(inv), rows, D, _ptr(dx),
+                                          self._dt(dx), _stream()), "cxl_l2norm_bwd")
+        return dx
+
     # ---- retrieval ---------------------------------------------------------------------------------
     def rank_of_target(self, scores: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best)."""

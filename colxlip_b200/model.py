@@ -8,7 +8,49 @@ called directly for retrieval scoring.
 """
 from __future__ import annotations
 
+import torch
+from torch.autograd.function import once_differentiable
+
+from .kernels import default_kernels
 from .loss import compute_colbert_similarity_mean
+
+
+class _L2NormFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, out_dtype, kernels):
+        xc = x.detach()
+        if xc.dtype not in (torch.float32, torch.bfloat16):
+            xc = xc.float()
+        y, inv = kernels.l2norm_fwd(xc.contiguous(), out_dtype, save_inv=x.requires_grad)
+        if x.requires_grad:
+            ctx.save_for_backward(y, inv)
+        ctx.meta = (kernels, x.dtype)
+        return y
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        kernels, dt = ctx.meta
+        y, inv = ctx.saved_tensors
+        if g.dtype not in (torch.float32, torch.bfloat16):
+            g = g.float()
+        out_dt = dt if dt in (torch.float32, torch.bfloat16) else torch.float32
+        return kernels.l2norm_bwd(y, g.contiguous(), inv, out_dt).to(dt), None, None
+
+
+def normalize_tokens(x, out_dtype=None, kernels=None):
+    """F.normalize(x, dim=-1) as the reference applies it to the token / global embeddings
+    (model.py:551-554, 605-607), fused with the cast to the dtype the MaxSim kernels consume.
+
+    out_dtype=None: bfloat16 under CUDA autocast or for bf16 inputs (what torch.einsum at loss.py:34 would cast
+    its operand to), else x.dtype.  A bf16 result goes into ColClipLoss / compute_colbert_similarity without a
+    further pack pass, and into the feature all-gather at half the fp32 bytes.  x: [..., D], D % 8 == 0."""
+    k = kernels if kernels is not None else default_kernels()
+    if out_dtype is None:
+        autocast = x.is_cuda and torch.is_autocast_enabled("cuda")
+        bf = x.dtype == torch.bfloat16 or (autocast and torch.get_autocast_dtype("cuda") == torch.bfloat16)
+        out_dtype = torch.bfloat16 if bf else (x.dtype if x.dtype == torch.float32 else torch.float32)
+    return _L2NormFn.apply(x, out_dtype, k)
 
 
 class ColXLIPScoringMixin:
@@ -17,6 +59,11 @@ class ColXLIPScoringMixin:
     def compute_colbert_similarity(self, token_image_features, token_text_features):
         """[Bt,Bi] plain-mean MaxSim scores, values in [-1, 1] for normalised features."""
         return compute_colbert_similarity_mean(token_image_features, token_text_features)
+
+
+    @staticmethod
+    def normalize_tokens(x):
+        return normalize_tokens(x)
 
 
 def patch_colxlip(model_cls):

@@ -155,6 +155,20 @@ int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_d
                      float* dX, float* dscale_accum, void* stream);
 
 /*
+ * L2 normalisation of embedding rows fused with the cast to the operand dtype.  Replaces
+ * F.normalize(x, dim=-1) at the end of ColXLIP.encode_image / encode_text (model.py:551-554, 605-607) and the
+ * autocast copy einsum makes of its result (loss.py:34):
+ *   y[r,:] = x[r,:] / max(||x[r,:]||_2, 1e-12)       x [rows,D] f32|bf16 -> y [rows,D] bf16|f32, contiguous
+ *   inv_norm[r] = 1 / max(||x[r,:]||, 1e-12)         [rows] f32, kept for the backward (may be NULL: inference)
+ * and its backward  dx[r,:] = (g[r,:] - y[r,:] * <g[r,:], y[r,:]>) * inv_norm[r].
+ * D % 8 == 0; all row pointers 16-byte aligned.
+ */
+int cxl_l2norm_fwd(const void* x, int x_dtype, long long rows, int D, void* y, int y_dtype, float* inv_norm,
+                   void* stream);
+int cxl_l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const float* inv_norm, long long rows,
+                   int D, void* dx, int dx_dtype, void* stream);
+
+/*
  * Retrieval ranking: rank of the ground-truth column in every row of a score matrix
  * (number of entries strictly greater, ties broken by lower index first, as a stable
  * descending argsort does).  Replaces the per-row argsort loop of train.py:467-469.

@@ -89,6 +89,16 @@ class TorchRefKernels:
             dX = dX / (cnt + 1e-8)
         return dX, (t * X).sum().reshape(1)
 
+    def l2norm_fwd(self, x, out_dtype, save_inv=True):
+        xf = x.float()
+        inv = 1.0 / xf.norm(dim=-1).clamp_min(1e-12)
+        return (xf * inv[..., None]).to(out_dtype), (inv.reshape(-1) if save_inv else None)
+
+    def l2norm_bwd(self, y, g, inv, out_dtype):
+        yf, gf = y.float(), g.float()
+        dot = (yf * gf).sum(dim=-1, keepdim=True)
+        return ((gf - yf * dot) * inv.reshape(y.shape[:-1])[..., None]).to(out_dtype)
+
     def rank_of_target(self, scores, target):
         scores = scores.float()
         R, C = scores.shape

@@ -173,3 +173,26 @@ def test_grad_rows_world2_gloo(gwg):
             gr = torch.from_numpy(gr)
             assert (gr[lo:hi] - ref).abs().max() <= 1e-5 * ref.abs().max() + 1e-8, (rank, n)
             assert gr[:lo].abs().max() == 0 and gr[hi:].abs().max() == 0
+
+
+# ---- f-3 normalize_tokens (autograd wiring; the kernels themselves are checked on the GPU) ---------------
+@pytest.mark.parametrize("out_dtype", [None, torch.float32, torch.bfloat16])
+def test_normalize_tokens_wiring(out_dtype):
+    import torch.nn.functional as F
+    from colxlip_b200.model import normalize_tokens
+    g = torch.Generator().manual_seed(5)
+    x0 = torch.randn(4, 7, 16, generator=g) * 2
+    x0[0, 1] = 0
+    grad = torch.randn(4, 7, 16, generator=g)
+    x = x0.clone().requires_grad_()
+    y = normalize_tokens(x, out_dtype=out_dtype, kernels=TorchRefKernels())
+    assert y.dtype == (out_dtype or torch.float32)
+    y.backward(grad.to(y.dtype))
+    xr = x0.clone().requires_grad_()
+    F.normalize(xr, dim=-1).backward(grad.to(y.dtype).float())
+    tol = 1e-6 if y.dtype == torch.float32 else 1e-2
+    assert (y.float() - F.normalize(x0, dim=-1)).abs().max() <= max(tol, 4e-3 if y.dtype == torch.bfloat16 else 0)
+    assert (x.grad - xr.grad).abs().max() <= tol * xr.grad.abs().max()
+    assert x.grad.dtype == torch.float32
+    # no grad requested: nothing saved, plain tensor out
+    assert not normalize_tokens(x0, kernels=TorchRefKernels()).requires_grad
