@@ -26,6 +26,13 @@ __device__ __forceinline__ void ms_push(MS& a, float v) {
   }
 }
 
+// four values at once, branch-free: one rescale of the running sum + four exponentials (values are finite)
+__device__ __forceinline__ void ms_push4(MS& a, float v0, float v1, float v2, float v3) {
+  const float mn = fmaxf(fmaxf(a.m, fmaxf(v0, v1)), fmaxf(v2, v3));
+  a.s = a.s * expf(a.m - mn) + ((expf(v0 - mn) + expf(v1 - mn)) + (expf(v2 - mn) + expf(v3 - mn)));
+  a.m = mn;
+}
+
 // ---- row log-sum-exp: one CTA per row ----
 __global__ void __launch_bounds__(256) infonce_row_kernel(const float* __restrict__ X, const float* __restrict__ scale_p,
                                                           int B, int row0, float* __restrict__ row_lse,
@@ -33,13 +40,21 @@ __global__ void __launch_bounds__(256) infonce_row_kernel(const float* __restric
   const int m = blockIdx.x;
   const float scale = *scale_p;
   const float* x = X + static_cast<size_t>(m) * B;
-  MS acc{-INFINITY, 0.f};
+  MS acc{-INFINITY, 0.f}, acc2{-INFINITY, 0.f};
   const int nvec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) ? (B >> 2) : 0;
-  for (int i = threadIdx.x; i < nvec; i += blockDim.x) {
+  int i = threadIdx.x;
+  for (; i + static_cast<int>(blockDim.x) < nvec; i += 2 * blockDim.x) {     // two independent 16-byte loads in flight
     const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
-    ms_push(acc, scale * v.x); ms_push(acc, scale * v.y); ms_push(acc, scale * v.z); ms_push(acc, scale * v.w);
+    const float4 u = __ldg(reinterpret_cast<const float4*>(x) + i + blockDim.x);
+    ms_push4(acc, scale * v.x, scale * v.y, scale * v.z, scale * v.w);
+    ms_push4(acc2, scale * u.x, scale * u.y, scale * u.z, scale * u.w);
   }
-  for (int i = nvec * 4 + threadIdx.x; i < B; i += blockDim.x) ms_push(acc, scale * x[i]);
+  for (; i < nvec; i += blockDim.x) {
+    const float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
+    ms_push4(acc, scale * v.x, scale * v.y, scale * v.z, scale * v.w);
+  }
+  for (int j = nvec * 4 + threadIdx.x; j < B; j += blockDim.x) ms_push(acc, scale * x[j]);
+  acc = ms_combine(acc, acc2);
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) {
     MS other{__shfl_xor_sync(0xffffffffu, acc.m, o), __shfl_xor_sync(0xffffffffu, acc.s, o)};
@@ -68,7 +83,19 @@ __global__ void __launch_bounds__(128) infonce_col_partial_kernel(const float* _
   const int r1 = min(r0 + kColRowsPerBlock, B_loc);
   MS a[4] = {{-INFINITY, 0.f}, {-INFINITY, 0.f}, {-INFINITY, 0.f}, {-INFINITY, 0.f}};
   const bool vec = (c0 + 3 < B) && ((B & 3) == 0) && ((reinterpret_cast<uintptr_t>(X) & 15) == 0);
-  for (int r = r0; r < r1; ++r) {
+  int r = r0;
+  if (vec) {
+    for (; r + 4 <= r1; r += 4) {                       // four independent 16-byte loads in flight
+      float4 t[4];
+#pragma unroll
+      for (int j = 0; j < 4; ++j) t[j] = __ldg(reinterpret_cast<const float4*>(X + static_cast<size_t>(r + j) * B + c0));
+      ms_push4(a[0], scale * t[0].x, scale * t[1].x, scale * t[2].x, scale * t[3].x);
+      ms_push4(a[1], scale * t[0].y, scale * t[1].y, scale * t[2].y, scale * t[3].y);
+      ms_push4(a[2], scale * t[0].z, scale * t[1].z, scale * t[2].z, scale * t[3].z);
+      ms_push4(a[3], scale * t[0].w, scale * t[1].w, scale * t[2].w, scale * t[3].w);
+    }
+  }
+  for (; r < r1; ++r) {
     const float* x = X + static_cast<size_t>(r) * B + c0;
     float v[4];
     if (vec) {
@@ -116,17 +143,36 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
   const float* cn = cnt ? cnt + static_cast<size_t>(m) * B : nullptr;
   const int diag_c = row0 + m;
   float ds = 0.f;
-  for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B; c += gridDim.x * blockDim.x) {
-    const float xv = x[c];
+  auto one = [&](float xv, int c, float cl, float cnv) -> float {
     const float sx = scale * xv;
     // col_lse == nullptr: rows-only cross-entropy (ClipLoss local_loss, loss.py:144-146): softmax_row - delta
     float t = expf(sx - rl);
-    if (col_lse) t += expf(sx - col_lse[c]);
+    if (col_lse) t += expf(sx - cl);
     if (c == diag_c) t -= col_lse ? 2.f : 1.f;
     t *= coef;
     ds = fmaf(t, xv, ds);
     const float dxv = t * scale;
-    dx[c] = cn ? dxv / (cn[c] + 1e-8f) : dxv;      // with cnt: the MaxSim pair weight  dL/dS / (cnt + 1e-8)
+    return cn ? dxv / (cnv + 1e-8f) : dxv;            // with cnt: the MaxSim pair weight  dL/dS / (cnt + 1e-8)
+  };
+  // rows of X / dX / cnt are 16-byte aligned when the bases are and B % 4 == 0: four columns per thread and access
+  const bool vec = ((B & 3) == 0) && (((reinterpret_cast<uintptr_t>(X) | reinterpret_cast<uintptr_t>(dX) |
+                                        reinterpret_cast<uintptr_t>(cnt) | reinterpret_cast<uintptr_t>(col_lse)) & 15) == 0);
+  if (vec) {
+    const int nv = B >> 2;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nv; i += gridDim.x * blockDim.x) {
+      const float4 xv = *(reinterpret_cast<const float4*>(x) + i);
+      const float4 cl = col_lse ? __ldg(reinterpret_cast<const float4*>(col_lse) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      const float4 cv = cn ? __ldg(reinterpret_cast<const float4*>(cn) + i) : make_float4(0.f, 0.f, 0.f, 0.f);
+      float4 o;
+      o.x = one(xv.x, 4 * i, cl.x, cv.x);
+      o.y = one(xv.y, 4 * i + 1, cl.y, cv.y);
+      o.z = one(xv.z, 4 * i + 2, cl.z, cv.z);
+      o.w = one(xv.w, 4 * i + 3, cl.w, cv.w);
+      *(reinterpret_cast<float4*>(dx) + i) = o;
+    }
+  } else {
+    for (int c = blockIdx.x * blockDim.x + threadIdx.x; c < B; c += gridDim.x * blockDim.x)
+      dx[c] = one(x[c], c, col_lse ? col_lse[c] : 0.f, cn ? cn[c] : 0.f);
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) ds += __shfl_xor_sync(0xffffffffu, ds, o);

@@ -89,9 +89,20 @@ __global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __rest
   const int t = target[r];
   const float tv = row[static_cast<long long>(t) * col_stride];
   int cnt = 0;
-  for (int c = threadIdx.x; c < cols; c += blockDim.x) {
-    const float v = row[static_cast<long long>(c) * col_stride];
-    cnt += (v > tv) || (v == tv && c < t);
+  if (col_stride == 1 && (cols & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
+    for (int i = threadIdx.x; i < (cols >> 2); i += blockDim.x) {          // contiguous rows: 16-byte loads
+      const float4 v = __ldg(reinterpret_cast<const float4*>(row) + i);
+      const int c = 4 * i;
+      cnt += (v.x > tv) || (v.x == tv && c < t);
+      cnt += (v.y > tv) || (v.y == tv && c + 1 < t);
+      cnt += (v.z > tv) || (v.z == tv && c + 2 < t);
+      cnt += (v.w > tv) || (v.w == tv && c + 3 < t);
+    }
+  } else {
+    for (int c = threadIdx.x; c < cols; c += blockDim.x) {
+      const float v = row[static_cast<long long>(c) * col_stride];
+      cnt += (v > tv) || (v == tv && c < t);
+    }
   }
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) cnt += __shfl_xor_sync(0xffffffffu, cnt, o);
@@ -105,9 +116,51 @@ __global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __rest
   }
 }
 
+// Same ranking for a TRANSPOSED view (row_stride == 1: consecutive rows are adjacent in memory, e.g. the t2i
+// direction scores.t() of compute_retrieval): lane <-> row so that every warp load is 32 consecutive floats;
+// the 8 warps of a CTA split the column range of the CTA's 32 rows.
+__global__ void __launch_bounds__(256) rank_of_target_tr_kernel(const float* __restrict__ scores, long long col_stride,
+                                                                int rows, int cols, const int* __restrict__ target,
+                                                                int* __restrict__ rank_out) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int r = blockIdx.x * 32 + lane;
+  const bool ok = r < rows;
+  const int t = ok ? target[r] : 0;
+  const float* base = scores + (ok ? r : 0);
+  const float tv = base[static_cast<long long>(t) * col_stride];
+  int cnt = 0;
+  int c = warp;
+  for (; c + 24 < cols; c += 32) {                      // four independent loads in flight per lane
+    float v[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) v[j] = __ldg(base + static_cast<long long>(c + 8 * j) * col_stride);
+#pragma unroll
+    for (int j = 0; j < 4; ++j) cnt += (v[j] > tv) || (v[j] == tv && c + 8 * j < t);
+  }
+  for (; c < cols; c += 8) {
+    const float v = base[static_cast<long long>(c) * col_stride];
+    cnt += (v > tv) || (v == tv && c < t);
+  }
+  __shared__ int part[8][32];
+  part[warp][lane] = cnt;
+  __syncthreads();
+  if (warp == 0 && ok) {
+    int s = 0;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) s += part[w][lane];
+    rank_out[r] = s;
+  }
+}
+
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                    const int* target, int* rank_out, cudaStream_t stream) {
   if (rows <= 0 || cols <= 0) return CXL_ERR_INVALID_ARG;
+  if (row_stride == 1 && col_stride != 1) {
+    rank_of_target_tr_kernel<<<(rows + 31) / 32, 256, 0, CXL_COUNTED(stream)>>>(scores, col_stride, rows, cols, target,
+                                                                               rank_out);
+    CXL_CUDA_CHECK(cudaGetLastError());
+    return CXL_OK;
+  }
   rank_of_target_kernel<<<rows, 256, 0, CXL_COUNTED(stream)>>>(scores, row_stride, col_stride, cols, target, rank_out);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;

@@ -246,3 +246,22 @@ def test_retrieval_loop_on_device(K):
     for k, v in ref.items():
         assert abs(metrics[k] - v) < 1e-9, k
     assert metrics["num_text_samples"] == n_img * caps and metrics["text_to_image_R@1"] > 0.5
+
+
+@pytest.mark.parametrize("R,C", [(5, 8), (33, 1000), (70, 1001), (257, 64), (40, 4096)])
+def test_rank_of_target_all_layouts(K, R, C):
+    """Contiguous rows (16-byte path / scalar path), the transposed view used for t2i, and a strided slice;
+    ties resolved by lower index as a stable descending argsort does (train.py:467-469)."""
+    from tests.ref_kernels import TorchRefKernels
+    ref = TorchRefKernels()
+    g = torch.Generator().manual_seed(R * C)
+    s = torch.randint(0, 50, (R, C), generator=g).float() / 7.0           # many exact ties
+    tgt = torch.randint(0, C, (R,), generator=g, dtype=torch.int32)
+    want = ref.rank_of_target(s, tgt)
+    sc = s.cuda()
+    assert torch.equal(K.rank_of_target(sc, tgt.cuda()).cpu(), want)
+    st = s.t().contiguous().cuda().t()                                     # same values, row_stride == 1
+    assert st.stride() == (1, R) and torch.equal(K.rank_of_target(st, tgt.cuda()).cpu(), want)
+    wide = torch.zeros(R, 2 * C + 3).cuda()
+    wide[:, 1:2 * C + 1:2] = sc                                            # col_stride 2, misaligned base
+    assert torch.equal(K.rank_of_target(wide[:, 1:2 * C + 1:2], tgt.cuda()).cpu(), want)
