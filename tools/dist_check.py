@@ -48,6 +48,50 @@ for gwg in (False, True):
     if e > 2e-4 * max(1e-3, abs(r_grads["logit_scale"].item())):
         ok = False
         print(f"rank {rank} gwg={gwg} logit_scale grad {ls.grad.item()} vs {r_grads['logit_scale'].item()}")
+# grad_rows (accumulation slice) over NCCL: the live slice's token gradients equal the full backward's, zeros elsewhere
+lo, hi = 16, 20         # lo * T = 1232 is a multiple of 16: the TMA-staged slice kernel, same bits as the full call
+for gwg in (False, True):
+    res = []
+    for rows in (None, (lo, hi)):
+        xs = [t[rank * b:(rank + 1) * b].clone().cuda().requires_grad_() for t in inputs]
+        ls = torch.tensor(1 / 0.07, device="cuda", requires_grad=True)
+        crit = ColClipLoss(alpha=0.5, rank=rank, world_size=world, gather_with_grad=gwg)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = crit(*xs, ls, **({"grad_rows": rows} if rows else {}))
+        loss.backward()
+        res.append([x.grad.float() for x in xs])
+    for full, part, n in zip(res[0], res[1], names):
+        err = (part[lo:hi] - full[lo:hi]).abs().max().item()
+        if err > 2e-5 * full.abs().max().item():
+            ok = False
+            print(f"rank {rank} gwg={gwg} grad_rows {n}: err {err:.3e}")
+        if n.startswith("token") and (part[:lo].abs().max().item() != 0 or part[hi:].abs().max().item() != 0):
+            ok = False
+            print(f"rank {rank} gwg={gwg} grad_rows {n}: non-zero outside the slice")
+
+# ClipLoss over NCCL against the REFERENCE's own 2-rank run (tests/golden/dist_w2.npz), world == 2 only
+if world == 2:
+    import numpy as np
+    from colxlip_b200 import ClipLoss
+    z = np.load(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "tests", "golden", "dist_w2.npz"))
+    gb = int(z["b"])
+    for local_loss in (0, 1):
+        for gwg in (0, 1):
+            xs = [torch.from_numpy(z[n])[rank * gb:(rank + 1) * gb].clone().cuda().requires_grad_()
+                  for n in ("image_features", "text_features")]
+            ls = torch.tensor(float(z["scale"]), device="cuda", requires_grad=True)
+            loss = ClipLoss(local_loss=bool(local_loss), gather_with_grad=bool(gwg), rank=rank, world_size=world)(*xs, ls)
+            loss.backward()
+            key = f"clip_l{local_loss}_g{gwg}_r{rank}"
+            bad = abs(loss.item() - float(z[key + "_loss"])) > 1e-5 * abs(float(z[key + "_loss"]))
+            for x, n in zip(xs, ("image_features", "text_features")):
+                ref = torch.from_numpy(z[f"{key}_g_{n}"])
+                bad |= (x.grad.cpu() - ref).abs().max().item() > 1e-5 * ref.abs().max().item() + 1e-9
+            bad |= abs(ls.grad.item() - float(z[key + "_g_logit_scale"])) > 2e-5 * max(1e-3, abs(float(z[key + "_g_logit_scale"])))
+            if bad:
+                ok = False
+                print(f"rank {rank} ClipLoss local_loss={local_loss} gwg={gwg}: mismatch vs the reference's rank-{rank} vectors")
+
 flag = torch.tensor([1 if ok else 0], device="cuda")
 dist.all_reduce(flag, op=dist.ReduceOp.MIN)
 if rank == 0:
