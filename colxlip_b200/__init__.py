@@ -1,9 +1,9 @@
 """colxlip_b200: B200-native (sm_100a) MaxSim contrastive scoring + loss, drop-in for
 lezhang7/colxlip's `colxlip.loss` API.  CUDA only; there is no CPU fallback."""
-from .loss import (ClipLoss, ColClipLoss, compute_colbert_similarity, compute_colbert_similarity_mean, gather_features,
+from .loss import (ClipLoss, ColClipAccumulation, ColClipLoss, compute_colbert_similarity, compute_colbert_similarity_mean, gather_features,
                    get_precision, set_precision)
 from .model import ColXLIPScoringMixin, normalize_tokens, patch_colxlip
 from .retrieval import compute_retrieval, maxsim_score_matrix, retrieval_on_split
 
-__all__ = ["ClipLoss", "ColClipLoss", "compute_colbert_similarity", "compute_colbert_similarity_mean", "gather_features",
+__all__ = ["ClipLoss", "ColClipAccumulation", "ColClipLoss", "compute_colbert_similarity", "compute_colbert_similarity_mean", "gather_features",
            "ColXLIPScoringMixin", "patch_colxlip", "normalize_tokens", "compute_retrieval", "maxsim_score_matrix", "retrieval_on_split", "set_precision", "get_precision"]

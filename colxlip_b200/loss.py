@@ -240,61 +240,144 @@ class _ColClipLossFn(torch.autograd.Function):
     @staticmethod
     @once_differentiable
     def backward(ctx, g):
-        cfg = ctx.cfg
-        k = cfg["kernels"]
-        W, group = cfg["world_size"], cfg.get("group")
-        alpha, prec = float(cfg["alpha"]), cfg["prec"]
-        T, P, b, row0, dt_img, dt_txt, dt_timg, dt_ttxt, dt_ls, ls_shape = ctx.meta
-        (txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale, rl_g, cl_g, rl_t, cl_t) = ctx.saved_tensors
-        g = g.float()
-        coef_g = (g[0] + alpha * g[2]).reshape(1).contiguous()
-        coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
+        return _colclip_backward(ctx.saved_tensors, ctx.cfg, ctx.meta, g, ctx.needs_input_grad) + (None,)
 
-        # K3 gradient pass (also yields d logit_scale partials of this rank's rows)
-        w, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t, cnt=cnt)   # pair weights dL/dS / cnt
-        dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, rl_g, cl_g)
-        dscale = dscale_t + dscale_g
-        if W > 1:
-            dist.all_reduce(dscale, group=group)
 
-        need = ctx.needs_input_grad
-        d_txt = dG @ g_img if need[1] else None
-        d_img_all = dG.T @ g_txt if need[0] else None
-        mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
-        rows = cfg.get("grad_rows")
-        if rows is None:
-            # K2: token gradients from the saved argmax
-            dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
-                                                  need_txt=need[3], need_img=need[2])
-            # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
-            # reproduces the reference's x world_size (every rank back-propagates the same full loss).
-            dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
-        else:
-            # gradient-accumulation call (train.py:166-183): only samples lo..hi-1 of every rank's batch carry
-            # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items; the rest stays zero
-            lo, hi = rows
-            n = hi - lo
-            dtxt_tok = dimg_tok = None
-            if need[3]:
+def _colclip_backward(saved, cfg, meta, g, need):
+    """Gradients of losses[3] w.r.t. (image, text, token image, token text features, logit_scale) from the tensors the
+    forward saved.  cfg["grad_rows"] restricts the token gradients to one slice of the local batch (zeros elsewhere, or
+    just the slices of all four feature gradients when cfg["slice_out"] is set)."""
+    k = cfg["kernels"]
+    W, group = cfg["world_size"], cfg.get("group")
+    alpha, prec = float(cfg["alpha"]), cfg["prec"]
+    T, P, b, row0, dt_img, dt_txt, dt_timg, dt_ttxt, dt_ls, ls_shape = meta
+    (txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale, rl_g, cl_g, rl_t, cl_t) = saved
+    g = g.float()
+    coef_g = (g[0] + alpha * g[2]).reshape(1).contiguous()
+    coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
+
+    # K3 gradient pass (also yields d logit_scale partials of this rank's rows)
+    w, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t, cnt=cnt)   # pair weights dL/dS / cnt
+    dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, rl_g, cl_g)
+    dscale = dscale_t + dscale_g
+    if W > 1:
+        dist.all_reduce(dscale, group=group)
+
+    d_txt = dG @ g_img if need[1] else None
+    d_img_all = dG.T @ g_txt if need[0] else None
+    mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
+    rows = cfg.get("grad_rows")
+    if rows is None:
+        # K2: token gradients from the saved argmax
+        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
+                                              need_txt=need[3], need_img=need[2])
+        # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
+        # reproduces the reference's x world_size (every rank back-propagates the same full loss).
+        dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
+    else:
+        # gradient-accumulation call (train.py:166-183): only samples lo..hi-1 of every rank's batch carry
+        # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items; the rest stays zero
+        lo, hi = rows
+        n = hi - lo
+        dtxt_tok = dimg_tok = None
+        slice_out = bool(cfg.get("slice_out"))
+        if need[3]:
+            part = k.maxsim_bwd_dtxt_rows(img_op, argmax, w, b, lo, n, T, P, prec)
+            if slice_out:
+                dtxt_tok = part
+            else:
                 dtxt_tok = torch.zeros((b, T, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
-                dtxt_tok[lo:hi] = k.maxsim_bwd_dtxt_rows(img_op, argmax, w, b, lo, n, T, P, prec)
-            if need[2]:
-                parts = [k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
-                                      k_off=r * b + lo, n_img=n)[1] for r in range(W)]
-                home = _reduce_scatter_rows(torch.cat(parts) if W > 1 else parts[0], W, group)
+                dtxt_tok[lo:hi] = part
+        if need[2]:
+            parts = [k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
+                                  k_off=r * b + lo, n_img=n)[1] for r in range(W)]
+            home = _reduce_scatter_rows(torch.cat(parts) if W > 1 else parts[0], W, group)
+            if slice_out:
+                dimg_tok = home
+            else:
                 dimg_tok = torch.zeros((b, P, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
                 dimg_tok[lo:hi] = home
-        d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
+    d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
+    if rows is not None and cfg.get("slice_out"):
+        d_img = d_img[rows[0]:rows[1]] if d_img is not None else None
+        d_txt = d_txt[rows[0]:rows[1]] if d_txt is not None else None
 
-        def fin(x, dt):
-            if x is None:
-                return None
-            if mult != 1.0:
-                x = x * mult
-            return x.to(dt)
+    def fin(x, dt):
+        if x is None:
+            return None
+        if mult != 1.0:
+            x = x * mult
+        return x.to(dt)
 
-        d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[4] else None
-        return fin(d_img, dt_img), fin(d_txt, dt_txt), fin(dimg_tok, dt_timg), fin(dtxt_tok, dt_ttxt), d_ls, None
+    d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[4] else None
+    return fin(d_img, dt_img), fin(d_txt, dt_txt), fin(dimg_tok, dt_timg), fin(dtxt_tok, dt_ttxt), d_ls
+
+
+class _SavedForward:
+    """Stand-in for an autograd ctx: lets `_ColClipLossFn._forward` run outside autograd and keeps what it saves."""
+
+    def save_for_backward(self, *tensors):
+        self.saved_tensors = tensors
+
+
+class _AccumSliceFn(torch.autograd.Function):
+    """losses[3] of the shared forward, differentiable w.r.t. ONE sub-batch's live features and logit_scale."""
+
+    @staticmethod
+    def forward(ctx, image_features, text_features, token_image_features, token_text_features, logit_scale, state,
+                lo, hi):
+        ctx.state, ctx.rows = state, (lo, hi)
+        ctx.dtypes = (image_features.dtype, text_features.dtype, token_image_features.dtype,
+                      token_text_features.dtype, logit_scale.dtype, logit_scale.shape)
+        return state.losses.clone()
+
+    @staticmethod
+    @once_differentiable
+    def backward(ctx, g):
+        st = ctx.state
+        cfg = dict(st.fwd.cfg, grad_rows=ctx.rows, slice_out=True)
+        meta = st.fwd.meta[:4] + ctx.dtypes
+        return _colclip_backward(st.fwd.saved_tensors, cfg, meta, g, ctx.needs_input_grad) + (None, None, None)
+
+
+class ColClipAccumulation:
+    """Shared forward of one gradient-accumulation step (reference train.py:138-185).
+
+    The reference re-runs the loss on `cat(cached[:j] + [live_j] + cached[j+1:])` for every sub-batch j: accum_freq
+    full forwards (K1!) and backwards of which only sub-batch j's gradients survive.  When the model is deterministic
+    between the caching pass and the live pass (no dropout / stochastic depth -- the CLIP towers of the reference have
+    none), the live features equal the cached ones, so all accum_freq calls see the SAME logits: this object runs
+    K1 + K3 statistics ONCE on the cached features and `slice_loss(lo, hi, **model_out)` returns the loss dict for
+    sub-batch lo..hi-1 whose backward runs K3-grad + K2 on that slice only.  Over the whole step: one forward and
+    one backward's worth of K2 instead of accum_freq of each.  logit_scale receives the full-batch gradient in every
+    slice call, exactly as in the reference's loop.  Built by `ColClipLoss.accumulation(...)`.
+    """
+
+    def __init__(self, fwd: _SavedForward, losses: torch.Tensor, local_batch: int):
+        self.fwd, self.losses, self.local_batch = fwd, losses, local_batch
+
+    def slice_loss(self, lo, hi, image_features=None, text_features=None, token_image_features=None,
+                   token_text_features=None, logit_scale=None, logit_bias=None, output_dict=False, verify=False,
+                   **kwargs):
+        lo, hi = int(lo), int(hi)
+        if not (0 <= lo < hi <= self.local_batch):
+            raise ValueError("slice must satisfy 0 <= lo < hi <= local batch of the shared forward")
+        feats = (image_features, text_features, token_image_features, token_text_features)
+        if any(f.shape[0] != hi - lo for f in feats):
+            raise ValueError("live features must hold exactly hi - lo samples")
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        if verify:   # debugging aid: the live token features must reproduce the cached operands bit for bit
+            T, P = self.fwd.meta[0], self.fwd.meta[1]
+            k, prec = self.fwd.cfg["kernels"], self.fwd.cfg["prec"]
+            live = k.prepare(token_text_features, T, prec)
+            if not torch.equal(live, self.fwd.saved_tensors[0][lo:hi]):
+                raise RuntimeError("live text-token features differ from the cached ones: the model is not "
+                                   "deterministic between passes; use ColClipLoss.forward(grad_rows=...) instead")
+        losses = _AccumSliceFn.apply(*feats, logit_scale, self, lo, hi)
+        if output_dict:
+            return {"global_contrastive_loss": losses[0], "token_contrastive_loss": losses[1], "total_loss": losses[2]}
+        return losses[2]
 
 
 class ColClipLoss(nn.Module):
@@ -367,6 +450,32 @@ class ColClipLoss(nn.Module):
             logits_per_image = logits_per_image + 2 * logit_bias
         return {"logits_per_image": logits_per_image, "logits_per_text": logits_per_image.T,
                 "logits_per_image_token": logits_per_text_token.T, "logits_per_text_token": logits_per_text_token}
+
+    def accumulation(self, image_features, text_features, token_image_features, token_text_features, logit_scale,
+                     **kwargs) -> "ColClipAccumulation":
+        """Shared no-grad forward over the CACHED features of all accum_freq sub-batches (this rank's, concatenated in
+        order): see ColClipAccumulation.  logit_scale is read by value."""
+        if self.world_size > 1:
+            if self.use_horovod:
+                raise RuntimeError("horovod is not supported by colxlip_b200")
+            if self.local_loss:
+                raise NotImplementedError
+        _check_tokens(token_image_features, token_text_features)
+        if token_image_features.shape[0] != token_text_features.shape[0]:
+            raise ValueError("ColClipLoss needs as many texts as images (labels are the diagonal)")
+        if not torch.is_tensor(logit_scale):
+            logit_scale = torch.tensor(float(logit_scale), device=image_features.device)
+        cfg = {
+            "kernels": self._k(), "world_size": self.world_size, "rank": self.rank, "group": self._group,
+            "alpha": self.alpha, "gather_with_grad": self.gather_with_grad,
+            "prec": _select_precision(token_image_features, token_text_features),
+        }
+        fwd = _SavedForward()
+        with torch.no_grad(), torch.autocast(token_image_features.device.type, enabled=False):
+            losses = _ColClipLossFn._forward(fwd, image_features.detach(), text_features.detach(),
+                                             token_image_features.detach(), token_text_features.detach(),
+                                             logit_scale.detach(), cfg)
+        return ColClipAccumulation(fwd, losses, token_text_features.shape[0])
 
     def forward(
             self,

@@ -265,3 +265,45 @@ def test_rank_of_target_all_layouts(K, R, C):
     wide = torch.zeros(R, 2 * C + 3).cuda()
     wide[:, 1:2 * C + 1:2] = sc                                            # col_stride 2, misaligned base
     assert torch.equal(K.rank_of_target(wide[:, 1:2 * C + 1:2], tgt.cuda()).cpu(), want)
+
+
+@pytest.mark.parametrize("autocast", [False, True])
+def test_accumulation_shared_forward_on_device(autocast):
+    """ColClipLoss.accumulation + slice_loss == the per-sub-batch full forward/backward of the reference's loop
+    (train.py:166-183) when live features equal the cached ones; K1 runs once."""
+    from colxlip_b200 import ColClipLoss
+    from colxlip_b200.kernels import default_kernels
+    B, P, T, D, acc = 32, 196, 16, 128, 4
+    sub = B // acc
+    feats = [t.cuda() for t in O.synth_inputs(B, P, T, D, seed=78, pad_text=True)]
+    ctx = (lambda: torch.autocast("cuda", dtype=torch.bfloat16)) if autocast else nullcontext
+    crit = ColClipLoss(alpha=0.5)
+    # reference-style loop through the plain forward
+    ls_ref = torch.tensor(1 / 0.07, device="cuda", requires_grad=True)
+    want = []
+    for j in range(acc):
+        lo, hi = j * sub, (j + 1) * sub
+        live = [t[lo:hi].clone().requires_grad_() for t in feats]
+        cat = [torch.cat([t[:lo], l, t[hi:]]) for t, l in zip(feats, live)]
+        with ctx():
+            total = crit(*cat, ls_ref)
+        total.backward()
+        want.append([l.grad for l in live])
+    K = default_kernels()
+    n0 = K.launches()
+    ls = torch.tensor(1 / 0.07, device="cuda", requires_grad=True)
+    with ctx():
+        state = crit.accumulation(*feats, ls)
+    fwd_launches = K.launches() - n0
+    for j in range(acc):
+        lo, hi = j * sub, (j + 1) * sub
+        live = [t[lo:hi].clone().requires_grad_() for t in feats]
+        with ctx():
+            out = state.slice_loss(lo, hi, *live, ls, output_dict=True, verify=True)
+        assert abs(out["total_loss"].item() - total.item()) <= 1e-6 * abs(total.item())
+        out["total_loss"].backward()
+        for l, w_, n in zip(live, want[j], NAMES):
+            assert l.grad.dtype == w_.dtype and l.grad.shape == w_.shape
+            assert (l.grad.float() - w_.float()).abs().max() <= 2e-5 * w_.float().abs().max() + 1e-12, (j, n)
+    assert abs(ls.grad.item() - ls_ref.grad.item()) <= 1e-5 * abs(ls_ref.grad.item())
+    assert fwd_launches > 0

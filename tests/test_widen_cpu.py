@@ -133,7 +133,7 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, gwg, q):
+def _worker(rank, world, port, gwg, q, shared=False):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -145,19 +145,30 @@ def _worker(rank, world, port, gwg, q):
         xs = [t[sl].clone().requires_grad_() for t in feats]
         ls = torch.tensor(12.0, requires_grad=True)
         crit = L.ColClipLoss(alpha=0.4, gather_with_grad=gwg, rank=rank, world_size=world, kernels=TorchRefKernels())
-        crit(*xs, ls, grad_rows=(lo, hi)).backward()
-        q.put((rank, [x.grad.numpy().copy() for x in xs]))
+        if shared:      # ColClipLoss.accumulation: live slice tensors only
+            state = crit.accumulation(*[x.detach() for x in xs], ls)
+            live = [x.detach()[lo:hi].clone().requires_grad_() for x in xs]
+            state.slice_loss(lo, hi, *live, ls).backward()
+            grads = []
+            for x, l in zip(xs, live):
+                g = torch.zeros_like(x)
+                g[lo:hi] = l.grad
+                grads.append(g.numpy().copy())
+            q.put((rank, grads))
+        else:
+            crit(*xs, ls, grad_rows=(lo, hi)).backward()
+            q.put((rank, [x.grad.numpy().copy() for x in xs]))
     finally:
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("gwg", [False, True])
-def test_grad_rows_world2_gloo(gwg):
+@pytest.mark.parametrize("gwg,shared", [(False, False), (True, False), (False, True), (True, True)])
+def test_grad_rows_world2_gloo(gwg, shared):
     world, b, lo, hi = 2, 4, 1, 3
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, gwg, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, gwg, q, shared)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in range(world)]
@@ -196,3 +207,45 @@ def test_normalize_tokens_wiring(out_dtype):
     assert x.grad.dtype == torch.float32
     # no grad requested: nothing saved, plain tensor out
     assert not normalize_tokens(x0, kernels=TorchRefKernels()).requires_grad
+
+
+# ---- f-4, shared forward: one K1 for the whole accumulation step ------------------------------------------
+def test_accumulation_shared_forward_equals_reference_loop():
+    """The reference's loop (train.py:166-183) on the oracle vs ColClipLoss.accumulation + slice_loss."""
+    B, acc = 8, 4
+    sub = B // acc
+    feats = O.synth_inputs(B, 5, 4, 16, seed=51, pad_text=True)
+    # reference-style loop on the oracle: accum_freq full losses, each back-propagating into its live slice
+    ls_ref = torch.tensor(15.0, requires_grad=True)
+    ref_grads = [torch.zeros_like(t) for t in feats]
+    for j in range(acc):
+        lo, hi = j * sub, (j + 1) * sub
+        live = [t[lo:hi].clone().requires_grad_() for t in feats]
+        cat = [torch.cat([t[:lo], l, t[hi:]]) for t, l in zip(feats, live)]
+        total = O.ColClipLossOracle(0.6)(*cat, ls_ref)
+        total.backward()
+        for g, l in zip(ref_grads, live):
+            g[lo:hi] = l.grad
+    # shared forward
+    crit = L.ColClipLoss(alpha=0.6, kernels=TorchRefKernels())
+    ls = torch.tensor(15.0, requires_grad=True)
+    state = crit.accumulation(*feats, ls)
+    assert isinstance(state, L.ColClipAccumulation)
+    for j in range(acc):
+        lo, hi = j * sub, (j + 1) * sub
+        live = [t[lo:hi].clone().requires_grad_() for t in feats]
+        out = state.slice_loss(lo, hi, *live, ls, output_dict=True, verify=True)
+        assert set(out) == {"global_contrastive_loss", "token_contrastive_loss", "total_loss"}
+        assert abs(out["total_loss"].item() - total.item()) < 1e-5
+        out["total_loss"].backward()
+        for l, g, n in zip(live, ref_grads, ("img", "txt", "tok_img", "tok_txt")):
+            assert l.grad.shape == l.shape
+            torch.testing.assert_close(l.grad, g[lo:hi], rtol=1e-4, atol=1e-7, msg=n)
+    assert abs(ls.grad.item() - ls_ref.grad.item()) <= 1e-5 * abs(ls_ref.grad.item())      # accum_freq x d scale
+    # a model that is NOT deterministic between passes is caught by verify=True
+    bad = [t[0:sub].clone() for t in feats]
+    bad[3] = bad[3] * 0.5
+    with pytest.raises(RuntimeError):
+        state.slice_loss(0, sub, *bad, ls, verify=True)
+    with pytest.raises(ValueError):
+        state.slice_loss(0, sub + 1, *[t[0:sub] for t in feats], ls)

@@ -75,10 +75,20 @@ def main():
             kw = {"grad_rows": (lo, hi)} if use_rows else {}
             col(*cat, ls, **kw).backward()
 
+    def accum_shared():
+        state = col.accumulation(*feats, ls)
+        for j in range(acc):
+            lo, hi = j * sub, (j + 1) * sub
+            live = [t[lo:hi].clone().requires_grad_() for t in feats]
+            state.slice_loss(lo, hi, *live, ls).backward()
+
     ms_full = timed(lambda: accum_step(False), warm=1, it=3)
     ms_rows = timed(lambda: accum_step(True), warm=1, it=3)
     out.append({"what": f"accum_freq={acc} loop at B={B} (train.py:166-183), full backward each call", "ms": ms_full})
     out.append({"what": f"same loop with grad_rows (slice backward)", "ms": ms_rows, "speedup": ms_full / ms_rows})
+    ms_sh = timed(accum_shared, warm=1, it=3)
+    out.append({"what": "same step with ColClipLoss.accumulation (one shared forward + slice backwards)", "ms": ms_sh,
+                "speedup": ms_full / ms_sh})
     del feats
     # f-2 / cfg-4: 1000 images x 1000 captions of 248 tokens, plain-mean scorer + recall
     ti = F.normalize(torch.randn(1000, 196, 512, device="cuda", generator=g), dim=-1).to(torch.bfloat16)
