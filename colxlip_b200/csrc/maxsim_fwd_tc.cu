@@ -49,6 +49,14 @@ struct FwdTcParams {
   long long ld_arg;
   float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
   int exp_mode;          // experiments (env CXL_K1_EXP): bit0 = skip the epilogue scan (timing only, wrong results)
+  // Pair kernel, packed tiles (env CXL_K1_PACK=1; P % 16 != 0): instead of padding every image to round_up(P,16)
+  // columns, `pack_g` consecutive images (pack_g * P a multiple of 16) share pack_g tiles whose widths add up to
+  // pack_g * P exactly.  Tile t of a group starts at flat patch row pack_start[t] of the group and is pack_n[t]
+  // wide: image t from its column pack_start[t] - t*P on, followed by the first (< 16) columns of image t + 1,
+  // whose running max is carried into the next tile.  0 = padded tiles.
+  int pack_g;
+  uint16_t pack_start[16];
+  uint16_t pack_n[16];
 };
 
 struct __align__(8) FwdTcBarriers {
@@ -81,6 +89,17 @@ __device__ __forceinline__ void scan16(const uint32_t (&v)[16], int c0, int ncol
     }
   }
   if (lb > best) { best = lb; bidx = qoff + c0 + lj; }
+}
+
+// Packed tiles: the last `h` (< 16) columns of a tile's last chunk are patches 0..h-1 of the NEXT image.
+__device__ __forceinline__ void scan_head(const uint32_t (&v)[16], int h, float& best, int& bidx) {
+  best = -INFINITY;
+  bidx = 0;
+#pragma unroll
+  for (int j = 0; j < 16; ++j) {
+    const float x = __uint_as_float(v[j]);
+    if (j >= 16 - h && x > best) { best = x; bidx = j - (16 - h); }
+  }
 }
 
 __global__ void __launch_bounds__(kThreads, 1)
@@ -375,7 +394,11 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
       a_phase ^= 1;
       for (int j = j0; j < j1; ++j) {
-        const int row0 = j * p.p_stride + static_cast<int>(rank) * half_rows;
+        int row0 = j * p.p_stride + static_cast<int>(rank) * half_rows;
+        if (p.pack_g) {                                  // packed tiles: this CTA's half of tile t of group grp
+          const int grp = j / p.pack_g, t = j - grp * p.pack_g;
+          row0 = grp * p.pack_g * p.P + p.pack_start[t] + static_cast<int>(rank) * (p.pack_n[t] >> 1);
+        }
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_empty[stage]), phase ^ 1);
           const uint32_t full = smem_u32(&bars->b_full[stage]);
@@ -411,6 +434,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // both CTAs' epilogues drained this buffer
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * 256;
+        const uint32_t idesc_j = p.pack_g ? umma_idesc_bf16(2 * kBlockM, p.pack_n[j % p.pack_g]) : idesc;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_full[stage]), phase);
           tc_fence_after();
@@ -419,7 +443,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             const uint64_t db = desc_b0 + static_cast<uint64_t>(stage * b_step);
 #pragma unroll
             for (int k = 0; k < kBlockK / kUmmaK; ++k)
-              umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);   // +32 bytes per UMMA_K
+              umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc_j, (kb | k) != 0);   // +32 bytes per UMMA_K
             umma_commit_2cta(smem_u32(&bars->b_empty[stage]), 3);      // frees the ring slot in both CTAs
           }
           __syncwarp();
@@ -442,10 +466,15 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     const int row_in_tile = quad * 32 + lane;
     int buf = 0;
     uint32_t acc_phase = 0;
-    const int nchunks = (p.P + 15) >> 4;
-    const int c_split = (nchunks + 1) >> 1;
-    const int c_lo = upper ? c_split : 0;
-    const int c_hi = upper ? nchunks : c_split;
+    int nchunks = (p.P + 15) >> 4;
+    int c_split = (nchunks + 1) >> 1;
+    int c_lo = upper ? c_split : 0;
+    int c_hi = upper ? nchunks : c_split;
+    int col_off = 0;                                      // packed tiles: image column of the tile's first column
+    int head_n = 0;                                       // packed tiles: columns of the NEXT image at the tile's end
+    float carry_best = -INFINITY;                         // lower warp: max over the next image's head columns
+    int carry_idx = 0;
+    float2* xhead = reinterpret_cast<float2*>(bars + 1);  // [2][128], allocated only for packed tiles
     for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
       const int chunk = unit / p.num_m_tiles;
       const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
@@ -472,23 +501,41 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         const uint32_t cbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + buf * 256;
         float best = -INFINITY;
         int bidx = 0;
+        if (p.pack_g) {                                   // geometry of tile t = k % pack_g (units start at t = 0)
+          const int t = k % p.pack_g;
+          col_off = static_cast<int>(p.pack_start[t]) - t * p.P;
+          head_n = static_cast<int>(p.pack_start[t]) + static_cast<int>(p.pack_n[t]) - (t + 1) * p.P;
+          nchunks = p.pack_n[t] >> 4;
+          c_split = (nchunks + 1) >> 1;
+          c_lo = upper ? c_split : 0;
+          c_hi = upper ? nchunks : c_split;
+          if (!upper && col_off > 0) { best = carry_best; bidx = carry_idx; }   // columns 0..col_off-1 came first
+        }
+        float hbest = -INFINITY;
+        int hidx = 0;
         if (c_lo < c_hi) {
           uint32_t va[16], vb[16];
           tmem_ld16(cbase + c_lo * 16, va);
           for (int c = c_lo; c < ((p.exp_mode & 1) ? c_lo + 1 : c_hi); c += 2) {
             tmem_wait_ld16(va);
             if (c + 1 < c_hi) tmem_ld16(cbase + (c + 1) * 16, vb);
-            scan16(va, c * 16, p.P, 0, best, bidx);
+            scan16(va, c * 16 + col_off, p.P, 0, best, bidx);
             if (c + 1 < c_hi) {
               tmem_wait_ld16(vb);
               if (c + 2 < c_hi) tmem_ld16(cbase + (c + 2) * 16, va);
-              scan16(vb, (c + 1) * 16, p.P, 0, best, bidx);
+              scan16(vb, (c + 1) * 16 + col_off, p.P, 0, best, bidx);
             }
+          }
+          if (upper && head_n > 0) {                      // the tile's last chunk again: head of the next image
+            tmem_ld16(cbase + (nchunks - 1) * 16, va);
+            tmem_wait_ld16(va);
+            scan_head(va, head_n, hbest, hidx);
           }
         }
         tc_fence_before();
         if (upper) {
           // all tcgen05.ld of this warp have completed (wait::ld above): hand the accumulator back, pass the result on
+          if (p.pack_g) xhead[buf * 128 + row_in_tile] = make_float2(hbest, __int_as_float(hidx));
           bars->xchg[buf][row_in_tile] = make_float2(best, __int_as_float(bidx));
           __syncwarp();
           if (lane == 0) {
@@ -498,6 +545,11 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         } else {
           mbar_wait(smem_u32(&bars->xfull[buf]), acc_phase);
           const float2 o = bars->xchg[buf][row_in_tile];  // upper columns: wins only if strictly greater
+          if (p.pack_g) {
+            const float2 hv = xhead[buf * 128 + row_in_tile];
+            carry_best = hv.x;
+            carry_idx = __float_as_int(hv.y);
+          }
           __syncwarp();
           if (lane == 0) mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));   // also orders xchg reuse after this read
           if (o.x > best) { best = o.x; bidx = __float_as_int(o.y); }
@@ -657,6 +709,29 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
         if (static_cast<double>(u) >= 0.97 * static_cast<double>(waves * clusters)) break;
       }
       q.tiles_per_unit = (q.total_n_tiles + chunks2 - 1) / chunks2;
+      // packed tiles (opt-in, CXL_K1_PACK=1): groups of g images with g*P % 16 == 0 share g tiles without pad columns
+      int extra_smem = 0;
+      static const int pack_env = getenv("CXL_K1_PACK") ? atoi(getenv("CXL_K1_PACK")) : 0;
+      if (pack_env && P % 16 != 0) {
+        int g = 16;
+        for (int d = 1; d <= 16; d <<= 1)
+          if ((P * d) % 16 == 0) { g = d; break; }
+        bool ok = true;
+        int start = 0;
+        for (int t = 0; t < g; ++t) {
+          const int end = round_up((t + 1) * P, 16);
+          const int n = end - start;
+          ok = ok && n <= q.n_tile && n >= 32 && start - t * P >= 0 && start - t * P < 16;
+          q.pack_start[t] = static_cast<uint16_t>(start);
+          q.pack_n[t] = static_cast<uint16_t>(n);
+          start = end;
+        }
+        if (ok) {
+          q.pack_g = g;
+          q.tiles_per_unit = round_up(q.tiles_per_unit, g);     // every unit starts on a group boundary
+          extra_smem = 2 * 128 * static_cast<int>(sizeof(float2));
+        }
+      }
       chunks2 = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
       q.num_units = chunks2 * q.num_m_tiles;
       q.mean_mode = mean_mode;
@@ -671,7 +746,8 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       const size_t npairs2 = static_cast<size_t>(Bt) * Bi;
       CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
       if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs2 * sizeof(float), stream));
-      const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes;
+      if (overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem > max_smem) q.num_stages -= 1;
+      const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem;
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
       int ncl = q.num_units < clusters ? q.num_units : clusters;
       maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
