@@ -45,6 +45,8 @@ def normalize_tokens(x, out_dtype=None, kernels=None):
     out_dtype=None: bfloat16 under CUDA autocast or for bf16 inputs (what torch.einsum at loss.py:34 would cast
     its operand to), else x.dtype.  A bf16 result goes into ColClipLoss / compute_colbert_similarity without a
     further pack pass, and into the feature all-gather at half the fp32 bytes.  x: [..., D], D % 8 == 0."""
+    if x.dim() < 1 or x.shape[-1] % 8 != 0:
+        raise ValueError("normalize_tokens needs an embedding dimension that is a multiple of 8 (16-byte row accesses)")
     k = kernels if kernels is not None else default_kernels()
     if out_dtype is None:
         autocast = x.is_cuda and torch.is_autocast_enabled("cuda")

@@ -207,6 +207,10 @@ def test_normalize_tokens_wiring(out_dtype):
     assert x.grad.dtype == torch.float32
     # no grad requested: nothing saved, plain tensor out
     assert not normalize_tokens(x0, kernels=TorchRefKernels()).requires_grad
+    with pytest.raises(ValueError):
+        normalize_tokens(torch.randn(3, 12), kernels=TorchRefKernels())
+    with pytest.raises(RuntimeError):           # product backend refuses CPU tensors: no CPU fallback
+        normalize_tokens(x0)
 
 
 # ---- f-4, shared forward: one K1 for the whole accumulation step ------------------------------------------
