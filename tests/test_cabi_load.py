@@ -87,3 +87,28 @@ def test_sass_is_blackwell_native():
     for mnem in ("UTCHMMA", "LDTM", "UTMALDG"):
         assert mnem in out.stdout, mnem
     assert "HGMMA" not in out.stdout
+
+
+def test_header_is_plain_c_and_a_c_program_links_the_library(tmp_path):
+    """include/colxlip_b200.h compiles as C99 and examples/cabi_probe.c (no device needed) links and runs against
+    libcolxlip_b200.so -- the boundary carries no C++ or torch types."""
+    import shutil
+    import subprocess
+    gcc = shutil.which("gcc")
+    if gcc is None:
+        pytest.skip("gcc not available")
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    from colxlip_b200 import _lib
+    _lib.load()
+    hdr = os.path.join(root, "include", "colxlip_b200.h")
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-Werror", "-fsyntax-only", "-x", "c", hdr],
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    exe = str(tmp_path / "cabi_probe")
+    libdir = os.path.dirname(_lib.LIB_PATH)
+    r = subprocess.run([gcc, "-std=c99", "-Wall", "-I" + os.path.join(root, "include"),
+                        os.path.join(root, "examples", "cabi_probe.c"), "-o", exe, "-L" + libdir, "-lcolxlip_b200",
+                        "-Wl,-rpath," + libdir], capture_output=True, text=True)
+    assert r.returncode == 0, r.stderr
+    r = subprocess.run([exe], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0 and "CABI_PROBE OK" in r.stdout, r.stdout + r.stderr
