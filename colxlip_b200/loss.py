@@ -176,6 +176,12 @@ def _reduce_scatter_rows(x_all: torch.Tensor, world_size: int, group) -> torch.T
     return out
 
 
+def _dimg_all_max_bytes() -> int:
+    """Largest fp32 dImg partial over all gathered images the multi-GPU backward materialises in one piece
+    (CXL_DIMG_GATHER_MAX_GB, default 48); above it the images are processed one home rank at a time."""
+    return int(float(os.environ.get("CXL_DIMG_GATHER_MAX_GB", "48")) * (1 << 30))
+
+
 def _round_like_gemm_input(x: torch.Tensor, prec: str) -> torch.Tensor:
     """fp32 copy of the global features as the GEMM sees them (bf16-rounded on the bf16 path)."""
     x = x.detach()
@@ -267,7 +273,20 @@ def _colclip_backward(saved, cfg, meta, g, need):
     d_img_all = dG.T @ g_txt if need[0] else None
     mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
     rows = cfg.get("grad_rows")
-    if rows is None:
+    if rows is None and W > 1 and need[2] and img_op.shape[0] * P * img_op.shape[2] * 4 > _dimg_all_max_bytes():
+        # The fp32 dImg partial over ALL gathered images would not fit next to the argmax (cfg-5: 116 GB per rank):
+        # go through the images one home rank at a time -- K2 on the shard of rank r (k_off / n_img), SUM-reduce to r.
+        dtxt_tok = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=True, need_img=False)[0] \
+            if need[3] else None
+        dimg_tok = None
+        for r in range(W):
+            part = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
+                                k_off=r * b, n_img=b)[1]
+            dist.reduce(part, dst=(dist.get_global_rank(group, r) if group is not None else r), group=group)
+            if r == cfg["rank"]:
+                dimg_tok = part
+            del part
+    elif rows is None:
         # K2: token gradients from the saved argmax
         dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
                                               need_txt=need[3], need_img=need[2])

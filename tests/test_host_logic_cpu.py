@@ -119,7 +119,9 @@ def _free_port():
     return p
 
 
-def _worker(rank, world, port, gather_with_grad, q):
+def _worker(rank, world, port, gather_with_grad, q, shard_dimg=False):
+    if shard_dimg:
+        os.environ["CXL_DIMG_GATHER_MAX_GB"] = "0"      # force the one-home-rank-at-a-time dImg path (cfg-5 sized runs)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -139,13 +141,13 @@ def _worker(rank, world, port, gather_with_grad, q):
         dist.destroy_process_group()
 
 
-@pytest.mark.parametrize("gather_with_grad", [False, True])
-def test_world2_gloo_matches_global_batch(gather_with_grad):
+@pytest.mark.parametrize("gather_with_grad,shard_dimg", [(False, False), (True, False), (False, True), (True, True)])
+def test_world2_gloo_matches_global_batch(gather_with_grad, shard_dimg):
     world, b = 2, 4
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, world, port, gather_with_grad, q)) for r in range(world)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, gather_with_grad, q, shard_dimg)) for r in range(world)]
     for p in procs:
         p.start()
     res = [q.get(timeout=120) for _ in range(world)]
