@@ -11,7 +11,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 BUILD = os.path.join(PKG_DIR, "csrc", "build")
 LIB_PATH = os.path.join(PKG_DIR, "libcolxlip_b200.so")
-SOURCES = ["api.cu", "maxsim_fwd_tc.cu", "maxsim_fwd_f32.cu", "maxsim_bwd.cu", "maxsim_bwd_v2.cu", "infonce.cu", "misc.cu", "l2norm.cu"]
+SOURCES = ["api.cu", "maxsim_fwd_tc.cu", "maxsim_fwd_f32.cu", "maxsim_bwd.cu", "maxsim_bwd_v2.cu", "maxsim_bwd_dimg4.cu", "infonce.cu", "misc.cu", "l2norm.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 
@@ -27,20 +27,36 @@ def needs_build() -> bool:
     if not os.path.exists(LIB_PATH):
         return True
     t = os.path.getmtime(LIB_PATH)
-    deps = [os.path.join(CSRC, s) for s in SOURCES] + [os.path.join(CSRC, "common.cuh"),
+    deps = [os.path.join(CSRC, s) for s in SOURCES] + [os.path.join(CSRC, "common.cuh"), os.path.join(CSRC, "bwd_v2_common.cuh"),
                                                       os.path.join(PKG_DIR, "..", "include", "colxlip_b200.h")]
     return any(os.path.getmtime(d) > t for d in deps)
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
+    """Compile + link under an exclusive file lock (torchrun starts one process per GPU: without the lock every
+    rank that sees a stale library would run nvcc into the same object files and a sibling could dlopen a
+    half-written .so).  Objects and the library are written under temporary names and renamed into place."""
     if not force and not needs_build():
         return LIB_PATH
+    import fcntl
     nvcc = _nvcc()
     os.makedirs(BUILD, exist_ok=True)
+    with open(os.path.join(BUILD, ".lock"), "w") as lock:
+        fcntl.flock(lock, fcntl.LOCK_EX)
+        try:
+            if not force and not needs_build():          # another process built it while we waited
+                return LIB_PATH
+            return _build_locked(nvcc, verbose)
+        finally:
+            fcntl.flock(lock, fcntl.LOCK_UN)
+
+
+def _build_locked(nvcc: str, verbose: bool) -> str:
+    tag = f".{os.getpid()}.tmp"
 
     def compile_one(src: str) -> str:
         obj = os.path.join(BUILD, src.replace(".cu", ".o"))
-        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        cmd = [nvcc, *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj + tag]
         if verbose:
             cmd.insert(1, "-Xptxas")
             cmd.insert(2, "-v")
@@ -49,15 +65,17 @@ def build_library(force: bool = False, verbose: bool = False) -> str:
             sys.stderr.write(r.stdout + r.stderr)
         if r.returncode != 0:
             raise RuntimeError(f"nvcc failed on {src}")
+        os.replace(obj + tag, obj)
         return obj
 
     with ThreadPoolExecutor(max_workers=len(SOURCES)) as ex:
         objs = list(ex.map(compile_one, SOURCES))
-    cmd = [nvcc, "-shared", "-o", LIB_PATH, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
+    cmd = [nvcc, "-shared", "-o", LIB_PATH + tag, *objs, "-gencode", "arch=compute_100a,code=sm_100a"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)
         raise RuntimeError("link failed")
+    os.replace(LIB_PATH + tag, LIB_PATH)
     return LIB_PATH
 
 

@@ -17,7 +17,7 @@
 //   dImg: also a gather with static accumulators: a pre-pass sorts every 512-row super-tile of text rows by
 //         argmax patch (per image), then CTA = (2 images, 64-wide D slice) streams the super-tiles + the list
 //         blocks through a TMA ring and each quarter warp walks the row lists of the patches it owns.
-#include "common.cuh"
+#include "bwd_v2_common.cuh"
 
 namespace cxl {
 
@@ -50,32 +50,6 @@ struct __align__(8) V2Barriers {
   uint64_t empty[8];
 };
 
-
-__device__ __forceinline__ uint32_t pack_entry_lo(float w, uint32_t hi16) {
-  return (hi16 << 16) | static_cast<uint32_t>(__bfloat16_as_ushort(__float2bfloat16_rn(w)));
-}
-
-// acc[0..7] += bf16x8(v) * bf16(low half of e)
-__device__ __forceinline__ void fhfma8_lo(float (&a)[8], const uint4& v, uint32_t e) {
-  asm("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"
-      "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"
-      "mov.b32 {wl, wh}, %12;\n\t"
-      "fma.rn.f32.bf16 %0, x0, wl, %0;\n\t fma.rn.f32.bf16 %1, x1, wl, %1;\n\t"
-      "fma.rn.f32.bf16 %2, x2, wl, %2;\n\t fma.rn.f32.bf16 %3, x3, wl, %3;\n\t"
-      "fma.rn.f32.bf16 %4, x4, wl, %4;\n\t fma.rn.f32.bf16 %5, x5, wl, %5;\n\t"
-      "fma.rn.f32.bf16 %6, x6, wl, %6;\n\t fma.rn.f32.bf16 %7, x7, wl, %7;\n\t}"
-      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])
-      : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e));
-}
-
-__device__ __forceinline__ uint4 lds128(uint32_t addr) {
-  uint4 v;
-  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr));
-  return v;
-}
-__device__ __forceinline__ void sts32(uint32_t addr, uint32_t v) {
-  asm volatile("st.shared.b32 [%0], %1;" ::"r"(addr), "r"(v) : "memory");
-}
 
 // ------------------------------------------------------------------------------------------------
 // dTxt
@@ -559,7 +533,7 @@ static EncodeTiledFnV2 encode_fn_v2() {
 }
 
 // [rows, D] bf16 row-major, box = box_cols x box_rows, no swizzle (rows land densely, box_cols*2 bytes apart)
-static int make_tmap_plain(CUtensorMap* out, const void* base, long long rows, int D, int box_cols, int box_rows) {
+int make_tmap_plain(CUtensorMap* out, const void* base, long long rows, int D, int box_cols, int box_rows) {
   EncodeTiledFnV2 fn = encode_fn_v2();
   if (fn == nullptr) return CXL_ERR_CUDA;
   cuuint64_t gdim[2] = {static_cast<cuuint64_t>(D), static_cast<cuuint64_t>(rows)};
@@ -576,9 +550,9 @@ static int make_tmap_plain(CUtensorMap* out, const void* base, long long rows, i
   return CXL_OK;
 }
 
-static int round_up_i(int x, int m) { return (x + m - 1) / m * m; }
+int round_up_i(int x, int m) { return (x + m - 1) / m * m; }
 
-static int env_int(const char* name, int dflt) {
+int env_int(const char* name, int dflt) {
   const char* s = getenv(name);
   return (s != nullptr && *s != 0) ? atoi(s) : dflt;
 }
@@ -673,6 +647,31 @@ static bool stream_path_covers(const void* txt, const void* img, int Bt, int T, 
   return true;
 }
 
+
+// ---- dImg v4 (maxsim_bwd_dimg4.cu) ----
+static int max_optin_smem() {
+  int dev = 0, v = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess) return 232448;
+  if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess || v <= 0) return 232448;
+  return v;
+}
+// dImg generation: 3 (default) = 512-row super-tiles + per-patch row lists; 4 (CXL_DIMG_V=4) = staggered long walks +
+// pre-padded step tables (maxsim_bwd_dimg4.cu).  Both are bit-identical; v4 measured within +-2 % of v3
+// (profiles/r4a_dimg_v4_ab.txt), so v3 stays the default.
+static bool use_dimg4(int P) { return env_int("CXL_DIMG_V", 3) == 4 && dimg4_covers(P); }
+// images per chunk for `budget_bytes` of scratch: whole waves of the gather kernel (1 CTA per SM, D/64 CTAs per image group)
+static long long dimg4_cap(const Dimg4Geom& g, int Bi, int D, long long budget_bytes) {
+  long long cap = (budget_bytes - 256) / dimg4_bytes_per_image(g);
+  if (cap >= Bi) return Bi;
+  int a = num_sms(), b = D / 64;
+  while (b != 0) { const int t = a % b; a = b; b = t; }      // a = gcd(SMs, D/64)
+  const long long groups_per_wave = num_sms() / a;
+  const long long per_wave = groups_per_wave * g.nimg;
+  if (cap >= per_wave) cap = cap / per_wave * per_wave;
+  else cap = cap / g.nimg * g.nimg;
+  return cap;
+}
+
 // dImg plan: kernel variant (consumer warps x patches per quarter warp x images per CTA), list-block geometry and
 // how many images' row lists fit `budget_bytes` of scratch (whole waves of the gather kernel when chunking)
 struct DimgPlan {
@@ -708,6 +707,12 @@ static long long dimg_budget_bytes() {
 // preferred workspace of maxsim_bwd_stream for this shape (0: none needed / shape not on the fast path)
 size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D) {
   if (D % 128 != 0 || P > 576 || T < 8 || static_cast<long long>(Bt) * T >= (1LL << 31)) return 0;
+  if (use_dimg4(P)) {
+    const Dimg4Geom g = dimg4_geom(static_cast<long long>(Bt) * T, P, max_optin_smem());
+    long long cap = dimg4_cap(g, Bi, D, dimg_budget_bytes());
+    if (cap < g.nimg) cap = g.nimg < Bi ? g.nimg : Bi;
+    return static_cast<size_t>(cap * dimg4_bytes_per_image(g) + 256);
+  }
   DimgPlan d = dimg_plan(Bt, Bi, T, P, dimg_budget_bytes());
   if (d.cap < d.nimg) d.cap = d.nimg;
   return static_cast<size_t>(d.cap * d.per_img);
@@ -741,7 +746,38 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
     rc = P > 256 ? launch_dtxt_v2<15, true>(img, p, max_smem, stream) : launch_dtxt_v2<15, false>(img, p, max_smem, stream);
     if (rc != CXL_OK) return rc;
   }
-  if (dimg != nullptr) {
+  if (dimg != nullptr && use_dimg4(P)) {
+    const Dimg4Geom g = dimg4_geom(p.rows, P, max_smem);
+    const long long budget = ws != nullptr ? static_cast<long long>(ws_bytes) : dimg_budget_bytes();
+    long long cap = dimg4_cap(g, Bi, D, budget);
+    const long long min_cap = g.nimg < Bi ? g.nimg : Bi;
+    void* scratch = ws;
+    if (ws != nullptr) {
+      if (cap < min_cap) return CXL_ERR_WORKSPACE;
+    } else {
+      if (cap < min_cap) cap = min_cap;
+      for (;;) {
+        const cudaError_t ae = cudaMallocAsync(&scratch, static_cast<size_t>(cap * dimg4_bytes_per_image(g) + 256), stream);
+        if (ae == cudaSuccess) break;
+        (void)cudaGetLastError();
+        if (ae != cudaErrorMemoryAllocation || cap <= min_cap) {
+          set_cuda_error(ae, "cudaMallocAsync (dImg step tables)");
+          return CXL_ERR_CUDA;
+        }
+        cap = (cap / 2 + g.nimg - 1) / g.nimg * g.nimg;
+      }
+    }
+    rc = launch_dimg_v4(txt, argmax, ld_arg, w, Bt, Bi, T, P, D, ld_pairs, k_off, dimg, accumulate_img, g, scratch, cap,
+                        max_smem, stream);
+    if (ws == nullptr) {
+      const cudaError_t fe = cudaFreeAsync(scratch, stream);
+      if (rc == CXL_OK && fe != cudaSuccess) {
+        set_cuda_error(fe, "cudaFreeAsync (dImg step tables)");
+        rc = CXL_ERR_CUDA;
+      }
+    }
+    if (rc != CXL_OK) return rc;
+  } else if (dimg != nullptr) {
     DimgPlan d = dimg_plan(Bt, Bi, T, P, ws != nullptr ? static_cast<long long>(ws_bytes) : dimg_budget_bytes());
     p.n_st = d.n_st;
     p.hdr_words = d.hdr_words;

@@ -48,7 +48,10 @@ struct FwdTcParams {
   void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
   long long ld_arg;
   float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
-  int exp_mode;          // experiments (env CXL_K1_EXP): bit0 = skip the epilogue scan (timing only, wrong results)
+#ifdef CXL_EXPERIMENTS
+  int exp_mode;          // timing experiments, compiled only with -DCXL_EXPERIMENTS (env CXL_K1_EXP): bit0 = skip the
+                         // epilogue scan (WRONG results); release builds carry no such switch
+#endif
   // Pair kernel, packed tiles (env CXL_K1_PACK=1; P % 16 != 0): instead of padding every image to round_up(P,16)
   // columns, `pack_g` consecutive images (pack_g * P a multiple of 16) share pack_g tiles whose widths add up to
   // pack_g * P exactly.  Tile t of a group starts at flat patch row pack_start[t] of the group and is pack_n[t]
@@ -516,7 +519,12 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         if (c_lo < c_hi) {
           uint32_t va[16], vb[16];
           tmem_ld16(cbase + c_lo * 16, va);
-          for (int c = c_lo; c < ((p.exp_mode & 1) ? c_lo + 1 : c_hi); c += 2) {
+#ifdef CXL_EXPERIMENTS
+          const int c_end = (p.exp_mode & 1) ? c_lo + 1 : c_hi;
+#else
+          const int c_end = c_hi;
+#endif
+          for (int c = c_lo; c < c_end; c += 2) {
             tmem_wait_ld16(va);
             if (c + 1 < c_hi) tmem_ld16(cbase + (c + 1) * 16, vb);
             scan16(va, c * 16 + col_off, p.P, 0, best, bidx);
@@ -737,7 +745,9 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       q.mean_mode = mean_mode;
       q.argmax_u16 = P > 256;
       q.S = S; q.cnt = cnt; q.argmax = argmax; q.ld_arg = ld_arg; q.dbg = nullptr;
+#ifdef CXL_EXPERIMENTS
       q.exp_mode = getenv("CXL_K1_EXP") ? atoi(getenv("CXL_K1_EXP")) : 0;
+#endif
       CUtensorMap tmA2, tmB2;
       int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM);
       if (rc2 != CXL_OK) return rc2;

@@ -87,6 +87,10 @@ __global__ void __launch_bounds__(256) rank_of_target_kernel(const float* __rest
   const int r = blockIdx.x;
   const float* row = scores + static_cast<long long>(r) * row_stride;
   const int t = target[r];
+  if (t < 0 || t >= cols) {                                // stale / sentinel index: no out-of-bounds read, rank -1
+    if (threadIdx.x == 0) rank_out[r] = -1;
+    return;
+  }
   const float tv = row[static_cast<long long>(t) * col_stride];
   int cnt = 0;
   if (col_stride == 1 && (cols & 3) == 0 && (reinterpret_cast<uintptr_t>(row) & 15) == 0) {
@@ -125,7 +129,9 @@ __global__ void __launch_bounds__(256) rank_of_target_tr_kernel(const float* __r
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int r = blockIdx.x * 32 + lane;
   const bool ok = r < rows;
-  const int t = ok ? target[r] : 0;
+  const int t_raw = ok ? target[r] : 0;
+  const bool t_ok = t_raw >= 0 && t_raw < cols;            // stale / sentinel index: no out-of-bounds read, rank -1
+  const int t = t_ok ? t_raw : 0;
   const float* base = scores + (ok ? r : 0);
   const float tv = base[static_cast<long long>(t) * col_stride];
   int cnt = 0;
@@ -148,7 +154,7 @@ __global__ void __launch_bounds__(256) rank_of_target_tr_kernel(const float* __r
     int s = 0;
 #pragma unroll
     for (int w = 0; w < 8; ++w) s += part[w][lane];
-    rank_out[r] = s;
+    rank_out[r] = t_ok ? s : -1;
   }
 }
 

@@ -226,7 +226,8 @@ class CudaKernels:
 
     # ---- retrieval ---------------------------------------------------------------------------------
     def rank_of_target(self, scores: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
-        """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best)."""
+        """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best; -1 where the target is
+        outside [0, C): the kernel never dereferences such an index, callers turn it into IndexError)."""
         dev = _require_cuda(scores, target)
         if scores.dtype != torch.float32:
             scores = scores.float()

@@ -67,11 +67,12 @@ class _MaxSimFn(torch.autograd.Function):
     """S[Bt,Bi] = pooled max-over-patches similarity; backward from the saved argmax (K1 + K2)."""
 
     @staticmethod
-    def forward(ctx, img_tok, txt_tok, mean_mode, prec, kernels):
+    def forward(ctx, img_tok, txt_tok, mean_mode, prec, kernels, grad_mode=True):
         k = kernels
         Bi, P, D = img_tok.shape
         Bt, T, _ = txt_tok.shape
-        need_grad = img_tok.requires_grad or txt_tok.requires_grad
+        # grad_mode = torch.is_grad_enabled() at the call site (always False in here): no argmax under no_grad
+        need_grad = bool(grad_mode and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]))
         txt_op = k.prepare(txt_tok, T, prec)
         img_op = k.prepare(img_tok, k.img_row_stride(P, prec), prec)
         S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, mean_mode, need_grad)
@@ -88,14 +89,14 @@ class _MaxSimFn(torch.autograd.Function):
         need_img, need_txt = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         w = k.pair_weights(dS, cnt, T, mean_mode)
         dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=need_txt, need_img=need_img)
-        return (dimg.to(img_dt) if need_img else None, dtxt.to(txt_dt) if need_txt else None, None, None, None)
+        return (dimg.to(img_dt) if need_img else None, dtxt.to(txt_dt) if need_txt else None, None, None, None, None)
 
 
 def _maxsim(token_image_features, token_text_features, mean_mode, kernels=None):
     _check_tokens(token_image_features, token_text_features)
     k = kernels if kernels is not None else default_kernels()
     prec = _select_precision(token_image_features, token_text_features)
-    return _MaxSimFn.apply(token_image_features, token_text_features, mean_mode, prec, k)
+    return _MaxSimFn.apply(token_image_features, token_text_features, mean_mode, prec, k, torch.is_grad_enabled())
 
 
 def compute_colbert_similarity(token_image_features, token_text_features):
@@ -196,6 +197,8 @@ class _ColClipLossFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, image_features, text_features, token_image_features, token_text_features, logit_scale, cfg):
         # precision is decided by cfg["prec"]; the few torch ops in here must not be re-cast by an ambient autocast
+        # validation / no_grad calls save nothing: no argmax buffer (82 GB at cfg-2) and no argmax stores in K1
+        cfg = dict(cfg, need_bwd=bool(cfg.get("grad_mode", True) and any(ctx.needs_input_grad[:5])))
         with torch.autocast(token_image_features.device.type, enabled=False):
             return _ColClipLossFn._forward(ctx, image_features, text_features, token_image_features,
                                            token_text_features, logit_scale, cfg)
@@ -218,7 +221,8 @@ class _ColClipLossFn(torch.autograd.Function):
         g_img = _all_gather_cat(_round_like_gemm_input(image_features, prec), W, group)
 
         # K1: token-level scores of this rank's texts against all images
-        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, MASKED, True)
+        need_bwd = bool(cfg.get("need_bwd", True))
+        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, MASKED, need_bwd)
         # global CLIP scores (plain library GEMM, fp32 accumulate) -- SURVEY 8 f-1
         G = g_txt @ g_img.T
 
@@ -236,8 +240,9 @@ class _ColClipLossFn(torch.autograd.Function):
         loss_g, loss_t = stats[0][2], stats[1][2]
         total = alpha * loss_g + (1.0 - alpha) * loss_t
 
-        ctx.save_for_backward(txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale,
-                              stats[0][0], stats[0][1], stats[1][0], stats[1][1])
+        if need_bwd:
+            ctx.save_for_backward(txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale,
+                                  stats[0][0], stats[0][1], stats[1][0], stats[1][1])
         ctx.cfg = cfg
         ctx.meta = (T, P, b, row0, image_features.dtype, text_features.dtype, token_image_features.dtype,
                     token_text_features.dtype, logit_scale.dtype, logit_scale.shape)
@@ -534,6 +539,7 @@ class ColClipLoss(nn.Module):
             if not (0 <= lo < hi <= token_text_features.shape[0]):
                 raise ValueError("grad_rows must satisfy 0 <= lo < hi <= local batch")
             cfg["grad_rows"] = (lo, hi)
+        cfg["grad_mode"] = torch.is_grad_enabled()         # autograd.Function.forward itself always runs with grad off
         losses = _ColClipLossFn.apply(image_features, text_features, token_image_features, token_text_features,
                                       logit_scale, cfg)
         global_contrastive_loss, token_contrastive_loss, total_loss = losses[0], losses[1], losses[2]

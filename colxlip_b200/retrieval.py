@@ -6,7 +6,7 @@ by one rank-of-target kernel launch per direction (cxl_rank_of_target).
 from __future__ import annotations
 
 import math
-from typing import Dict, Sequence
+from typing import Dict
 
 import numpy as np
 import torch
@@ -25,24 +25,52 @@ def _report(ranks: np.ndarray, name: str) -> Dict[str, float]:
     }
 
 
-def compute_retrieval(similarity_scores, txt2img: Sequence[int], img2txt: Sequence[Sequence[int]], kernels=None):
-    """similarity_scores: [N_img, N_txt] (i2t) or a tuple (i2t, t2i) as in the reference."""
+def _by_position(x, n: int, what: str):
+    """The reference indexes txt2img / img2txt by POSITION (`txt2img[index]`, train.py:469,489): dicts keyed
+    0..n-1 (what remap_indices returns) and sequences are both accepted."""
+    if isinstance(x, dict):
+        try:
+            return [x[i] for i in range(n)]
+        except KeyError as e:
+            raise KeyError(f"compute_retrieval: {what} has no entry for position {e.args[0]} (expected keys 0..{n - 1})") from e
+    x = list(x)
+    if len(x) != n:
+        raise ValueError(f"compute_retrieval: {what} has {len(x)} entries for {n} score rows")
+    return x
+
+
+def compute_retrieval(similarity_scores, txt2img, img2txt, kernels=None):
+    """similarity_scores: [N_img, N_txt] (i2t) or a tuple (i2t, t2i) as in the reference (train.py:457-508).
+    txt2img: position -> gallery image index; img2txt: position -> list of caption indices (dicts keyed by
+    position or sequences).  An image without captions keeps the reference's sentinel rank 1e10; an index
+    outside the score matrix raises IndexError (the reference's `torch.where(...)[0][0]` does)."""
     k = kernels if kernels is not None else default_kernels()
     if isinstance(similarity_scores, tuple):
         i2t, t2i = similarity_scores
     else:
         i2t, t2i = similarity_scores, similarity_scores.t()
     dev = i2t.device
-    t2i_ranks = k.rank_of_target(t2i, torch.as_tensor(list(txt2img), dtype=torch.int32, device=dev))
+    n_txt, n_gal = t2i.shape
+    n_img, n_cap = i2t.shape
+    t_tgt = np.asarray([int(v) for v in _by_position(txt2img, n_txt, "txt2img")], dtype=np.int64)
+    if t_tgt.size and (t_tgt.min() < 0 or t_tgt.max() >= n_gal):
+        raise IndexError(f"compute_retrieval: txt2img holds an image index outside [0, {n_gal})")
+    caps = [[int(c) for c in x] for x in _by_position(img2txt, n_img, "img2txt")]
+    for x in caps:
+        if any(c < 0 or c >= n_cap for c in x):
+            raise IndexError(f"compute_retrieval: img2txt holds a caption index outside [0, {n_cap})")
+    t2i_ranks = k.rank_of_target(t2i, torch.as_tensor(t_tgt, dtype=torch.int32, device=dev))
     # image -> text: best (lowest) rank over the image's ground-truth captions
-    width = max(len(x) for x in img2txt)
+    width = max((len(x) for x in caps), default=0)
+    has_cap = np.asarray([len(x) > 0 for x in caps], dtype=bool)
     best = None
     for j in range(width):
-        tgt = torch.as_tensor([x[min(j, len(x) - 1)] for x in img2txt], dtype=torch.int32, device=dev)
+        tgt = torch.as_tensor([x[min(j, len(x) - 1)] if x else 0 for x in caps], dtype=torch.int32, device=dev)
         r = k.rank_of_target(i2t, tgt)
         best = r if best is None else torch.minimum(best, r)
     t2i_np = t2i_ranks.cpu().numpy().astype(np.float64)
-    i2t_np = best.cpu().numpy().astype(np.float64)
+    i2t_np = best.cpu().numpy().astype(np.float64) if best is not None else np.zeros(n_img)
+    i2t_np = np.where(has_cap, i2t_np, 1e10)                       # train.py:485: `rank = 1e10` when the loop is empty
     return {**_report(t2i_np, "text_to_image"), **_report(i2t_np, "image_to_text")}
 
 
@@ -122,9 +150,7 @@ def retrieval_on_split(keyword, model, txt_loader, img_loader, img2txt_dict, txt
         scores, img_ids = compute_similarity_scores_maxsim(m, img_loader, all_text_tokens, device, input_dtype,
                                                            autocast, kernels)
         new_img2txt, new_txt2img = remap_indices(img_ids, cap_ids, img2txt_dict, txt2img_dict)
-        n_txt = scores.shape[1]
-        retrieval_metrics = compute_retrieval(scores, [new_txt2img[c] for c in range(n_txt)],
-                                              [new_img2txt[i] for i in range(scores.shape[0])], kernels=kernels)
+        retrieval_metrics = compute_retrieval(scores, new_txt2img, new_img2txt, kernels=kernels)
     if keyword != '':
         keyword = keyword + '_'
         retrieval_metrics = {keyword + k: v for k, v in retrieval_metrics.items()}

@@ -172,6 +172,7 @@ int cxl_l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const
  * Retrieval ranking: rank of the ground-truth column in every row of a score matrix
  * (number of entries strictly greater, ties broken by lower index first, as a stable
  * descending argsort does).  Replaces the per-row argsort loop of train.py:467-469.
+ * A target outside [0, cols) is not dereferenced; its rank is -1 (the reference raises IndexError there).
  */
 int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                        const int* target /*[rows]*/, int* rank_out /*[rows]*/, void* stream);

@@ -216,6 +216,55 @@ def maxsim_closed_form_grads(img_tok, txt_tok, dS, mode: int = MASKED, round_w_b
     return dtxt, dimg
 
 
+def maxsim_closed_form_grads_by_text(img_tok, txt_tok, w, arg):
+    """Same sums as maxsim_closed_form_grads for a GIVEN pair weight w [Bt,Bi] and argmax [Bt,Bi,T], one text at
+    a time with vectorised gathers / index_add (runs on whatever device the inputs live on; used by the GPU
+    tests at sizes where the double Python loop would take hours).  fp32 throughout."""
+    Bi, P, D = img_tok.shape
+    Bt, T, _ = txt_tok.shape
+    img32, txt32 = img_tok.float(), txt_tok.float()
+    flat_img = img32.reshape(Bi * P, D)
+    dtxt = torch.zeros_like(txt32)
+    dimg = torch.zeros(Bi * P, D, dtype=torch.float32, device=img_tok.device)
+    base = (torch.arange(Bi, device=img_tok.device) * P)[:, None]                  # [Bi,1]
+    for m in range(Bt):
+        idx = (base + arg[m]).reshape(-1)                                          # [Bi*T] flat patch rows
+        picked = flat_img[idx].view(Bi, T, D)
+        dtxt[m] = torch.einsum("k,ktd->td", w[m], picked)                          # sum_k w[m,k] img[k,q*]
+        contrib = (w[m][:, None, None] * txt32[m][None]).reshape(Bi * T, D)        # w[m,k] txt[m,n]
+        dimg.index_add_(0, idx, contrib)
+    return dtxt, dimg.view(Bi, P, D)
+
+
+def loss_and_grads_blockwise(image_features, text_features, token_image_features, token_text_features,
+                             logit_scale: float, alpha: float = 0.5, round_w_bf16: bool = False):
+    """loss_and_grads (loss.py:271-296 + autograd) WITHOUT the [Bt,Bi,T,P] tensor: the token scores come from
+    maxsim_rowmax, the InfoNCE halves go through autograd on the [B,B] matrices, and the token-feature gradients
+    through the closed form.  Device-agnostic: the GPU parity tests evaluate it on the B200 at B = 1024, where
+    the plain restatement would need 63 GB per copy of the similarity tensor.
+    Returns (losses, grads, extras) with extras = {S, cnt, arg, dS}."""
+    dev = token_image_features.device
+    img = image_features.detach().clone().float().requires_grad_()
+    txt = text_features.detach().clone().float().requires_grad_()
+    ti, tt = token_image_features.detach().float(), token_text_features.detach().float()
+    ls = torch.tensor(float(logit_scale), device=dev, requires_grad=True)
+    mx, arg = maxsim_rowmax(ti, tt)
+    nz = (mx != 0).float().sum(dim=2)
+    S = (mx.sum(dim=2) / (nz + 1e-8)).requires_grad_()
+    g = infonce_pair(ls * img @ txt.T)
+    t = infonce_pair(ls * S)
+    total = alpha * g + (1 - alpha) * t
+    total.backward()
+    w = S.grad / (nz + 1e-8)
+    if round_w_bf16:
+        w = w.to(torch.bfloat16).float()
+    dtxt, dimg = maxsim_closed_form_grads_by_text(ti, tt, w, arg)
+    losses = {"global_contrastive_loss": g.detach(), "token_contrastive_loss": t.detach(), "total_loss": total.detach()}
+    grads = {"image_features": img.grad, "text_features": txt.grad, "token_image_features": dimg,
+             "token_text_features": dtxt, "logit_scale": ls.grad}
+    return losses, grads, {"S": S.detach(), "cnt": nz, "arg": arg, "dS": S.grad}
+
+
 def gather_scaling(gather_with_grad: bool, world_size: int) -> float:
     """Local-feature gradient = this factor x the single-process slice."""
     return float(world_size) if gather_with_grad else 1.0
@@ -238,7 +287,7 @@ def compute_retrieval(similarity_scores: torch.Tensor, txt2img: Sequence[int],
         order = torch.argsort(row, descending=True)
         pos = torch.empty_like(order)
         pos[order] = torch.arange(order.numel())
-        i2t_ranks[i] = min(int(pos[j]) for j in img2txt[i])
+        i2t_ranks[i] = min((int(pos[j]) for j in img2txt[i]), default=1e10)      # train.py:485: rank = 1e10
 
     def rep(r, name):
         return {f"{name}_R@1": float((r < 1).mean()), f"{name}_R@5": float((r < 5).mean()),

@@ -68,6 +68,32 @@ def _worker(rank, port, q):
             for x, n in zip(xs, ("image_features", "text_features", "token_image_features", "token_text_features")):
                 out[key + "_g_" + n] = x.grad.numpy().copy()
             out[key + "_g_logit_scale"] = ls.grad.item()
+        # public gather_features / ColClipLoss.get_logits at world_size 2 (loss.py:48-92, 223-269): the gathered
+        # tensors, the four logit matrices, and the local gradients of a seeded linear functional of them
+        gw = torch.Generator().manual_seed(SEED + 100)
+        w_img = torch.randn(B_LOC * WORLD, D, generator=gw)
+        w_txt = torch.randn(B_LOC * WORLD, D, generator=gw)
+        w_lpi = torch.randn(B_LOC * WORLD, B_LOC * WORLD, generator=gw)
+        w_lpt = torch.randn(B_LOC * WORLD, B_LOC * WORLD, generator=gw)
+        for gwg in (False, True):
+            xs = [t[sl].clone().requires_grad_() for t in feats[:2]]
+            ai, at = ref.gather_features(xs[0], xs[1], local_loss=False, gather_with_grad=gwg, rank=rank,
+                                         world_size=WORLD)
+            ((ai * w_img).sum() + (at * w_txt).sum()).backward()
+            key = f"gather_g{int(gwg)}_r{rank}"
+            out[key + "_all_image_features"] = ai.detach().numpy().copy()
+            out[key + "_all_text_features"] = at.detach().numpy().copy()
+            out[key + "_g_image_features"] = xs[0].grad.numpy().copy()
+            out[key + "_g_text_features"] = xs[1].grad.numpy().copy()
+            xs = [t[sl].clone().requires_grad_() for t in feats]
+            crit = ref.ColClipLoss(gather_with_grad=gwg, rank=rank, world_size=WORLD, alpha=ALPHA)
+            lg = crit.get_logits(*xs, torch.tensor(SCALE))
+            ((lg["logits_per_image"] * w_lpi).sum() + (lg["logits_per_text_token"] * w_lpt).sum()).backward()
+            key = f"logits_g{int(gwg)}_r{rank}"
+            for k, v in lg.items():
+                out[key + "_" + k] = v.detach().numpy().copy()
+            for x, n in zip(xs, ("image_features", "text_features", "token_image_features", "token_text_features")):
+                out[key + "_g_" + n] = x.grad.numpy().copy()
         q.put(out)
     finally:
         dist.destroy_process_group()

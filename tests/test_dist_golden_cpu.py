@@ -121,6 +121,57 @@ def _worker(rank, world, port, q):
             for x, n in zip(xs, NAMES):
                 out[key + "_g_" + n] = x.grad.numpy().copy()
             out[key + "_g_logit_scale"] = ls.grad.item()
+        # the PUBLIC gather_features / ColClipLoss.get_logits (reference loss.py:48-92, 223-269) at world_size 2:
+        # gathered tensors, the four logit matrices, and local gradients of a seeded linear functional of them
+        # (the generator applied the same contiguous-grad hook to torch.distributed.nn.all_gather)
+        import torch.distributed.nn as dnn
+        orig = dnn.all_gather
+
+        def all_gather_contig(t, *a, **k):
+            outs = orig(t, *a, **k)
+            for o in outs:
+                o.register_hook(lambda g: g.contiguous())
+            return outs
+
+        dnn.all_gather = all_gather_contig
+        torch.distributed.nn.all_gather = all_gather_contig
+        B, D = world * b, int(z["D"])
+        gw = torch.Generator().manual_seed(int(z["seed"]) + 100)
+        w_img, w_txt = torch.randn(B, D, generator=gw), torch.randn(B, D, generator=gw)
+        w_lpi, w_lpt = torch.randn(B, B, generator=gw), torch.randn(B, B, generator=gw)
+        for gwg in (0, 1):
+            xs = [t.clone().requires_grad_() for t in feats[:2]]
+            ai, at = L.gather_features(xs[0], xs[1], local_loss=False, gather_with_grad=bool(gwg), rank=rank,
+                                       world_size=world)
+            ((ai * w_img).sum() + (at * w_txt).sum()).backward()
+            key = f"gather_g{gwg}_r{rank}"
+            out[key + "_all_image_features"] = ai.detach().numpy().copy()
+            out[key + "_all_text_features"] = at.detach().numpy().copy()
+            out[key + "_g_image_features"] = xs[0].grad.numpy().copy()
+            out[key + "_g_text_features"] = xs[1].grad.numpy().copy()
+            xs = [t.clone().requires_grad_() for t in feats]
+            crit = L.ColClipLoss(alpha=alpha, gather_with_grad=bool(gwg), rank=rank, world_size=world,
+                                 kernels=TorchRefKernels())
+            lg = crit.get_logits(*xs, torch.tensor(scale))
+            ((lg["logits_per_image"] * w_lpi).sum() + (lg["logits_per_text_token"] * w_lpt).sum()).backward()
+            key = f"logits_g{gwg}_r{rank}"
+            for k, v in lg.items():
+                out[key + "_" + k] = v.detach().numpy().copy()
+            for x, n in zip(xs, NAMES):
+                out[key + "_g_" + n] = x.grad.numpy().copy()
+        if rank == 0:       # the reference raises for local_loss at world > 1 (loss.py:246-248); so does the mirror
+            crit = L.ColClipLoss(local_loss=True, rank=rank, world_size=world, kernels=TorchRefKernels())
+            try:
+                crit.get_logits(*feats, torch.tensor(scale))
+                out["local_loss_raises"] = 0
+            except NotImplementedError:
+                out["local_loss_raises"] = 1
+        else:               # keep the collectives of rank 0's call matched
+            crit = L.ColClipLoss(local_loss=True, rank=rank, world_size=world, kernels=TorchRefKernels())
+            try:
+                crit.get_logits(*feats, torch.tensor(scale))
+            except NotImplementedError:
+                pass
         q.put(out)
     finally:
         dist.destroy_process_group()
@@ -141,6 +192,7 @@ def test_world2_gloo_matches_reference_ranks():
     for p in procs:
         p.join(timeout=60)
         assert p.exitcode == 0
+    assert got.pop("local_loss_raises") == 1
     checked = 0
     for k, v in got.items():
         ref = z[k]
@@ -149,4 +201,4 @@ def test_world2_gloo_matches_reference_ranks():
         else:
             assert _close(v, ref), k
         checked += 1
-    assert checked == len([k for k in z.files if k.startswith(("clip_", "colclip_"))])
+    assert checked == len([k for k in z.files if k.startswith(("clip_", "colclip_", "gather_", "logits_"))])

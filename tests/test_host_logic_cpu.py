@@ -54,6 +54,40 @@ def test_individual_losses_are_differentiable():
     torch.testing.assert_close(xs[3].grad, ys[3].grad, rtol=1e-4, atol=1e-7)
 
 
+def test_no_backward_means_no_saved_argmax():
+    """Validation-style calls (torch.no_grad, or inputs that do not require grad) must not ask K1 for the argmax:
+    at cfg-2 that is an 82 GB buffer and extra store traffic for nothing."""
+    class Spy(TorchRefKernels):
+        def __init__(self):
+            self.saved = []
+
+        def maxsim_fwd(self, txt_op, img_op, T, P, prec, mean_mode, save_argmax):
+            self.saved.append(bool(save_argmax))
+            return super().maxsim_fwd(txt_op, img_op, T, P, prec, mean_mode, save_argmax)
+
+    img, txt, ti, tt = _inputs(5, 4, 3, 16, 6)
+    spy = Spy()
+    crit = L.ColClipLoss(kernels=spy)
+    a = crit(img, txt, ti, tt, torch.tensor(14.0))                        # nothing requires grad
+    xs = [t.clone().requires_grad_() for t in (img, txt, ti, tt)]
+    with torch.no_grad():
+        b = crit(*xs, torch.tensor(14.0))                                 # grad mode off
+    c = crit(*xs, torch.tensor(14.0))                                     # training call
+    c.backward()
+    assert spy.saved == [False, False, True]
+    assert abs(a.item() - c.item()) < 1e-6 and abs(b.item() - c.item()) < 1e-6
+    ls = torch.tensor(14.0, requires_grad=True)                           # only logit_scale trains: K3 grad needs S, cnt
+    spy.saved.clear()
+    crit(img, txt, ti, tt, ls).backward()
+    assert spy.saved == [True] and ls.grad is not None
+    # same for the bare scorer
+    spy.saved.clear()
+    with torch.no_grad():
+        L._maxsim(xs[2], xs[3], 0, spy)
+    L._maxsim(xs[2], xs[3], 0, spy).sum().backward()
+    assert spy.saved == [False, True]
+
+
 def test_total_loss_only_and_scalar_scale():
     img, txt, ti, tt = _inputs(5, 4, 3, 16, 5)
     t = L.ColClipLoss(kernels=TorchRefKernels())(img, txt, ti, tt, torch.tensor(14.0))
@@ -108,6 +142,46 @@ def test_compute_retrieval_matches_oracle():
     assert ours.keys() == ref.keys()
     for k in ref:
         assert abs(ours[k] - ref[k]) < 1e-9, k
+
+
+def test_compute_retrieval_takes_the_position_keyed_dicts_of_remap_indices():
+    """The reference's retrieval_on_split passes the dicts remap_indices returns and indexes them by position
+    (train.py:469,489); shuffled gallery ids, several captions per image, one image without captions."""
+    from colxlip_b200.retrieval import remap_indices
+    g = torch.Generator().manual_seed(3)
+    n_img, caps = 9, 2
+    s = torch.randn(n_img, n_img * caps, generator=g)
+    gallery_ids = torch.tensor([17, 3, 99, 42, 8, 23, 5, 61, 70])          # loader order -> original image id
+    img2txt = {int(i): [caps * j, caps * j + 1] for j, i in enumerate(gallery_ids.tolist())}
+    txt2img = {c: [int(gallery_ids[c // caps])] for c in range(n_img * caps)}
+    new_i2t, new_t2i = remap_indices(gallery_ids, torch.arange(n_img * caps), img2txt, txt2img)
+    assert isinstance(new_i2t, dict) and isinstance(new_t2i, dict)
+    ours = compute_retrieval(s, new_t2i, new_i2t, kernels=TorchRefKernels())
+    ref = O.compute_retrieval(s, new_t2i, new_i2t)
+    as_lists = compute_retrieval(s, [new_t2i[c] for c in range(n_img * caps)], [new_i2t[i] for i in range(n_img)],
+                                 kernels=TorchRefKernels())
+    for k in ref:
+        assert abs(ours[k] - ref[k]) < 1e-9 and ours[k] == as_lists[k], k
+    # an image without captions keeps the reference's sentinel rank (train.py:485) instead of raising
+    new_i2t[4] = []
+    ours = compute_retrieval(s, new_t2i, new_i2t, kernels=TorchRefKernels())
+    ref = O.compute_retrieval(s, new_t2i, new_i2t)
+    for k in ref:
+        assert abs(ours[k] - ref[k]) <= 1e-9 * max(1.0, abs(ref[k])), k
+    assert ours["image_to_text_mean_rank"] > 1e8
+
+
+def test_compute_retrieval_rejects_bad_indices():
+    s = torch.randn(4, 8, generator=torch.Generator().manual_seed(0))
+    good_t, good_i = [i // 2 for i in range(8)], [[2 * i, 2 * i + 1] for i in range(4)]
+    with pytest.raises(IndexError):
+        compute_retrieval(s, [0, 1, 2, 3, 4, 0, 0, 0], good_i, kernels=TorchRefKernels())      # image 4 of 4
+    with pytest.raises(IndexError):
+        compute_retrieval(s, good_t, [[0], [-1], [2], [3]], kernels=TorchRefKernels())         # stale -1 sentinel
+    with pytest.raises(ValueError):
+        compute_retrieval(s, good_t[:-1], good_i, kernels=TorchRefKernels())
+    with pytest.raises(KeyError):
+        compute_retrieval(s, {i + 100: v for i, v in enumerate(good_t)}, good_i, kernels=TorchRefKernels())   # caption-id keys
 
 
 # ---------------------------------------------------------------------------------------------

@@ -93,3 +93,22 @@ def test_compute_retrieval_identity():
     r = O.compute_retrieval(s, list(range(20)), [[i] for i in range(20)])
     assert r["text_to_image_R@1"] == 1.0 and r["image_to_text_R@1"] == 1.0
     assert r["text_to_image_mean_rank"] == 1.0
+
+
+def test_blockwise_oracle_equals_the_plain_restatement():
+    """loss_and_grads_blockwise (what the GPU tests evaluate on the device at B = 1024) against loss_and_grads
+    (autograd of the restatement that is pinned by the reference's own vectors above)."""
+    img, txt, ti, tt = O.synth_inputs(7, 9, 6, 16, seed=21, pad_text=True)
+    ti[2, 3] = ti[2, 5]                                   # duplicated patch: first index must win in both
+    l0, g0 = O.loss_and_grads(img, txt, ti, tt, 13.0, 0.3)
+    l1, g1, ex = O.loss_and_grads_blockwise(img, txt, ti, tt, 13.0, 0.3)
+    for k in l0:
+        assert abs(l0[k].item() - l1[k].item()) < 1e-6, k
+    for k in g0:
+        assert (g0[k] - g1[k]).abs().max().item() <= 1e-6 * max(1e-3, g0[k].abs().max().item()), k
+    assert torch.equal(ex["arg"], O.maxsim_rowmax(ti, tt)[1])
+    dS = torch.randn(7, 7, generator=torch.Generator().manual_seed(2))
+    a_txt, a_img = O.maxsim_closed_form_grads(ti, tt, dS)
+    cnt = (O.maxsim_rowmax(ti, tt)[0] != 0).float().sum(dim=2) + 1e-8
+    b_txt, b_img = O.maxsim_closed_form_grads_by_text(ti, tt, dS / cnt, ex["arg"])
+    assert (a_txt - b_txt).abs().max().item() < 1e-6 and (a_img - b_img).abs().max().item() < 1e-6
