@@ -655,10 +655,15 @@ static int max_optin_smem() {
   if (cudaDeviceGetAttribute(&v, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev) != cudaSuccess || v <= 0) return 232448;
   return v;
 }
-// dImg generation: 3 (default) = 512-row super-tiles + per-patch row lists; 4 (CXL_DIMG_V=4) = staggered long walks +
-// pre-padded step tables (maxsim_bwd_dimg4.cu).  Both are bit-identical; v4 measured within +-2 % of v3
-// (profiles/r4a_dimg_v4_ab.txt), so v3 stays the default.
-static bool use_dimg4(int P) { return env_int("CXL_DIMG_V", 3) == 4 && dimg4_covers(P); }
+// dImg generation: 3 = 512-row super-tiles + per-patch row lists; 4 = staggered long walks + pre-padded step tables
+// (maxsim_bwd_dimg4.cu).  Bit-identical results.  Measured on B200: P = 196 within +-2 % of each other
+// (profiles/r4a_dimg_v4_ab.txt) -> v3; P = 576, D = 768: v4 22 % faster (65.4 vs 83.9 ms at B = 2048, lists of 0.9
+// rows make v3's per-list overhead dominate) -> v4.  CXL_DIMG_V=3|4 forces one.
+static bool use_dimg4(int P) {
+  const int v = env_int("CXL_DIMG_V", 0);
+  if (!dimg4_covers(P)) return false;
+  return v == 4 || (v != 3 && P > 304);
+}
 // images per chunk for `budget_bytes` of scratch: whole waves of the gather kernel (1 CTA per SM, D/64 CTAs per image group)
 static long long dimg4_cap(const Dimg4Geom& g, int Bi, int D, long long budget_bytes) {
   long long cap = (budget_bytes - 256) / dimg4_bytes_per_image(g);

@@ -61,7 +61,17 @@ def test_backward_workspace_sizing(monkeypatch):
     assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 4, 196, 512, BF16) == 0
     # P > 200 / P > 300 variants: wider headers (300 -> 320 words, 19*4*8 = 608 words)
     assert lib.cxl_maxsim_bwd_workspace_bytes(64, 3, 77, 300, 128, BF16) == 3 * 10 * (320 * 4 + 2048)
+    monkeypatch.setenv("CXL_DIMG_V", "3")
     assert lib.cxl_maxsim_bwd_workspace_bytes(64, 3, 77, 576, 128, BF16) == 3 * 10 * (608 * 4 + 2048)
+    # P > 304 defaults to the v4 gather (staggered walks, step tables): 64*77 = 4928 rows, one image per CTA, sub-tiles of
+    # 768 rows (ring of 2 + two worst-case tables in 227 KB) -> 7 walks per image, each block = header (19 warps x
+    # 12 u16 = 464 B, rounded to 16) + 16 B per row + one padding step per phase (19*8) + the two-step end sentinel
+    monkeypatch.delenv("CXL_DIMG_V")
+    blk = 464 + 16 * 768 + 16 * 19 * 8 + 32
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 3, 77, 576, 128, BF16) == 3 * 7 * (blk + 2) + 256
+    monkeypatch.setenv("CXL_DIMG_V", "4")            # the v4 gather can be forced for P <= 304 too
+    assert lib.cxl_maxsim_bwd_workspace_bytes(64, 10, 77, 196, 512, BF16) not in (0, 10 * 10 * (224 * 4 + 2048))
+    monkeypatch.delenv("CXL_DIMG_V")
     monkeypatch.setenv("CXL_DIMG_SCRATCH_MB", "1")
     small = lib.cxl_maxsim_bwd_workspace_bytes(120, 23, 77, 196, 512, BF16)
     assert small <= 1 << 20 and small % (19 * (224 * 4 + 2048)) == 0 and small // (19 * 2944) == 18
