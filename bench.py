@@ -311,6 +311,18 @@ def run_gpu(args):
         dist.all_reduce(ems, op=dist.ReduceOp.MAX)
     e2e_ms = ems.item() / n_e2e
 
+    # ---- multi-rank numerics over the live NCCL group (outside every timed region): reference-executed vectors for
+    #      this world size + the tensor-core path against the single-GPU path (tools/dist_parity.py) ----
+    dist_parity = None
+    if world > 1 and not args.no_dist_parity:
+        try:
+            from tools.dist_parity import check as dist_parity_check
+            for x in feats + dev_in:
+                x.grad = None
+            dist_parity = dist_parity_check(rank, world, dev)
+        except Exception as e:                                  # never lose the measured line to the checker
+            dist_parity = {"ok": False, "world": world, "error": f"{type(e).__name__}: {e}"[:300]}
+
     if rank == 0:
         step_flops = 2.0 * B * B * T * P * D
         line = {
@@ -332,6 +344,8 @@ def run_gpu(args):
             "gpu_launches": launches,
             "clocks": clocks,
         }
+        if dist_parity is not None:
+            line["dist_parity"] = dist_parity
         if world == 1 and not args.no_cpu_baseline:
             line["cpu_baseline"] = cpu_baseline_obj(args.workload)
         emit(line)
@@ -351,6 +365,7 @@ def main():
     ap.add_argument("--k1-reps", type=int, default=2)
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-dist-parity", action="store_true")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: anything libraries print to fd 1 meanwhile (NCCL's version /
     # debug lines go to stdout) is diverted to stderr, and the result is written to the saved descriptor.

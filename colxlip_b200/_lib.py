@@ -40,6 +40,10 @@ SYMBOLS = {
     "cxl_maxsim_bwd_ws": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
     "cxl_maxsim_bwd_dtxt_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
+    "cxl_maxsim_bwd_shard": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                     c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
+    "cxl_maxsim_bwd_dtxt_rows_shard": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
+                                               c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
     "cxl_maxsim_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "cxl_maxsim_bwd_generic": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                        c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),

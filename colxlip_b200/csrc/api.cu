@@ -36,8 +36,8 @@ int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, in
                    float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
-               float* dtxt, float* dimg, int accumulate_img, int force_generic, void* ws, size_t ws_bytes,
-               cudaStream_t stream);
+               float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, int force_generic, void* ws,
+               size_t ws_bytes, cudaStream_t stream);
 size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D);
 int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
                  cudaStream_t stream);
@@ -143,7 +143,7 @@ static int bwd_entry(const void* txt, const void* img, const void* argmax, const
   if (rc != CXL_OK) return rc;
   const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
   return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), 0, w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off,
-                    dtxt, dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+                    dtxt, 0, dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
@@ -159,7 +159,45 @@ int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w
   // dTxt never reads the text operand; `img` stands in for the (unused) txt pointer of the shared dispatcher
   return maxsim_bwd(img, img, argmax, cxl_argmax_ld(Bt_total, T), static_cast<long long>(m0) * T,
                     w + static_cast<size_t>(m0) * ld_pairs, m_cnt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
-                    nullptr, 0, force_generic, nullptr, 0, static_cast<cudaStream_t>(stream));
+                    0, nullptr, 0, force_generic, nullptr, 0, static_cast<cudaStream_t>(stream));
+}
+
+// Shard-local operands: `argmax` is the shard's own buffer; the kernels index argmax rows and w columns with the same
+// k_off, so the argmax base is moved back by k_off rows (never dereferenced below the shard's first row).
+static const void* shard_argmax_base(const void* argmax, long long ld_arg, int P, int k_off) {
+  const uintptr_t back = static_cast<uintptr_t>(k_off) * static_cast<uintptr_t>(ld_arg) * (P > 256 ? 2u : 1u);
+  return reinterpret_cast<const void*>(reinterpret_cast<uintptr_t>(argmax) - back);
+}
+
+int cxl_maxsim_bwd_shard(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                         int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, int accumulate_txt,
+                         float* dimg, int accumulate_img, void* ws, size_t ws_bytes, void* stream) {
+  if (txt == nullptr || img == nullptr || argmax == nullptr || w == nullptr) return CXL_ERR_INVALID_ARG;
+  if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0 || k_off < 0) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const long long ld_arg = cxl_argmax_ld(Bt, T);
+  return maxsim_bwd(txt, img, shard_argmax_base(argmax, ld_arg, P, k_off), ld_arg, 0, w, Bt, Bi, T, P, D, dtype,
+                    p_stride, ld_pairs, k_off, dtxt, accumulate_txt, dimg, accumulate_img, 0, ws, ws_bytes,
+                    static_cast<cudaStream_t>(stream));
+}
+
+int cxl_maxsim_bwd_dtxt_rows_shard(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
+                                   int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
+                                   int accumulate_txt, void* stream) {
+  if (img == nullptr || argmax == nullptr || w == nullptr || dtxt == nullptr) return CXL_ERR_INVALID_ARG;
+  if (Bt_total <= 0 || m0 < 0 || m_cnt <= 0 || m0 + m_cnt > Bt_total || k_off < 0) return CXL_ERR_INVALID_ARG;
+  if (Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const long long ld_arg = cxl_argmax_ld(Bt_total, T);
+  return maxsim_bwd(img, img, shard_argmax_base(argmax, ld_arg, P, k_off), ld_arg, static_cast<long long>(m0) * T,
+                    w + static_cast<size_t>(m0) * ld_pairs, m_cnt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
+                    accumulate_txt, nullptr, 0, 0, nullptr, 0, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,

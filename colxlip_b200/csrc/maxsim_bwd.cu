@@ -45,6 +45,7 @@ struct BwdParams {
   float* dtxt;          // [Bt*T, D]
   float* dimg;          // [Bi*P, D]
   int accumulate_img;
+  int accumulate_txt;
 };
 
 __device__ __forceinline__ float pair_weight(const BwdParams& p, size_t pair) { return p.w[pair]; }
@@ -96,8 +97,14 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dtxt_kernel(const BwdParams p)
   if (d_ok) {
     float* out = p.dtxt + static_cast<size_t>(R) * p.D + d;
 #pragma unroll
-    for (int i = 0; i < V; i += 4)
-      *reinterpret_cast<float4*>(out + i) = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+    for (int i = 0; i < V; i += 4) {
+      float4 v = make_float4(acc[i], acc[i + 1], acc[i + 2], acc[i + 3]);
+      if (p.accumulate_txt) {
+        const float4 o = *reinterpret_cast<const float4*>(out + i);
+        v.x += o.x; v.y += o.y; v.z += o.z; v.w += o.w;
+      }
+      *reinterpret_cast<float4*>(out + i) = v;
+    }
   }
 }
 
@@ -148,21 +155,22 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
 
 int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                       const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
-                      float* dtxt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream);
+                      float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes,
+                      cudaStream_t stream);
 
 // arg_row_off != 0: txt / w / dtxt point at a slice of Bt texts whose first flat text-token row is `arg_row_off`
 // inside the forward's argmax rows (pitch ld_arg); only dTxt can be computed from a row slice.
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
-               float* dtxt, float* dimg, int accumulate_img, int force_generic, void* ws, size_t ws_bytes,
-               cudaStream_t stream) {
+               float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, int force_generic, void* ws,
+               size_t ws_bytes, cudaStream_t stream) {
   if (ld_pairs < Bi + k_off || k_off < 0) return CXL_ERR_INVALID_ARG;
   if (arg_row_off < 0 || ld_arg < arg_row_off + static_cast<long long>(Bt) * T) return CXL_ERR_INVALID_ARG;
   if (arg_row_off != 0 && dimg != nullptr) return CXL_ERR_INVALID_ARG;
   if (dtype == CXL_DTYPE_BF16 && !force_generic) {
     // fast path: TMA-staged streaming kernels; shapes it does not cover fall through to the generic kernels
     const int rc = maxsim_bwd_stream(txt, img, argmax, ld_arg, arg_row_off, w, Bt, Bi, T, P, D, p_stride, ld_pairs,
-                                     k_off, dtxt, dimg, accumulate_img, ws, ws_bytes, stream);
+                                     k_off, dtxt, accumulate_txt, dimg, accumulate_img, ws, ws_bytes, stream);
     if (rc != CXL_ERR_UNSUPPORTED) return rc;
   }
   const int V = dtype == CXL_DTYPE_BF16 ? 8 : 4;
@@ -173,7 +181,7 @@ int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long l
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D; p.p_stride = p_stride;
   p.ld_pairs = ld_pairs; p.k_off = k_off;
   p.argmax_u16 = P > 256;
-  p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img;
+  p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img; p.accumulate_txt = accumulate_txt;
 
   if (dtxt != nullptr) {
     const long long rows = static_cast<long long>(Bt) * T;

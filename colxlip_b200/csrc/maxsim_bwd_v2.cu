@@ -587,11 +587,12 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
   int kb = static_cast<int>((static_cast<long long>(env_int("CXL_DTXT_BLOCK_MB", 32)) << 20) / slab_bytes);
   if (kb < 8) kb = 8;
   const int Bi = p.Bi, k_off = p.k_off;
+  const int acc_first = p.accumulate_txt;          // shard calls continue from the previous shards' partial sums
   for (int k0 = 0; k0 < Bi; k0 += kb) {
     p.Bi = (Bi - k0 < kb) ? Bi - k0 : kb;
     p.k_off = k_off + k0;
     p.img_k0 = k0;
-    p.accumulate_txt = k0 > 0;
+    p.accumulate_txt = (k0 > 0) || acc_first;
     kern<<<grid, (NWC + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, p);
     CXL_CUDA_CHECK(cudaGetLastError());
   }
@@ -729,7 +730,8 @@ size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D) {
 // arg_row_off: first text-token row of this call inside the argmax rows (row-slice calls, dTxt only).
 int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                       const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
-                      float* dtxt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes, cudaStream_t stream) {
+                      float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes,
+                      cudaStream_t stream) {
   if (!stream_path_covers(txt, img, Bt, T, P, D)) return CXL_ERR_UNSUPPORTED;
   const int es = P > 256 ? 2 : 1;
   if ((arg_row_off * es) % 16 != 0) return CXL_ERR_UNSUPPORTED;     // bulk copies of argmax runs need 16 B alignment
@@ -741,7 +743,7 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D; p.p_stride = p_stride;
   p.rows = Bt * T;
   p.ld_pairs = ld_pairs; p.k_off = k_off; p.argmax_u16 = P > 256;
-  p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img;
+  p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img; p.accumulate_txt = accumulate_txt;
   int dev = 0, max_smem = 0;
   CXL_CUDA_CHECK(cudaGetDevice(&dev));
   CXL_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));

@@ -81,6 +81,11 @@ class CudaKernels:
         return torch.empty((Bi, ld), dtype=torch.uint8 if P <= 256 else torch.int16, device=dev)
 
     @staticmethod
+    def argmax_images(argmax: torch.Tensor, lo: int, hi: int) -> torch.Tensor:
+        """images lo..hi-1 of a saved argmax (image-major: a row range)"""
+        return argmax if (lo == 0 and hi == argmax.shape[0]) else argmax[lo:hi]
+
+    @staticmethod
     def argmax_as_text_major(argmax: torch.Tensor, Bt: int, T: int) -> torch.Tensor:
         """[Bi, ld] image-major -> [Bt, Bi, T] int64 (for checks against the oracle)."""
         Bi = argmax.shape[0]
@@ -142,6 +147,43 @@ class CudaKernels:
                                                  D, dt, ld, k_off, _ptr(dtxt), _ptr(dimg), 0, _ptr(ws), nws, _stream()),
                       "cxl_maxsim_bwd_ws")
         return dtxt, dimg
+
+    def maxsim_bwd_shard(self, txt_op, img_sh, arg_sh, w, k_off: int, T: int, P: int, prec: str,
+                         dtxt: Optional[torch.Tensor] = None, accumulate_txt: bool = False, need_img: bool = True):
+        """K2 for ONE SHARD of the images with shard-local operands (cxl_maxsim_bwd_shard): img_sh [n,p_stride,D] and
+        arg_sh [n, ld] are the shard's own buffers, w [Bt, ld_pairs] covers all images and the shard is its columns
+        [k_off, k_off+n).  `dtxt` [Bt,T,D] fp32 (optional) is overwritten, or added to when accumulate_txt.
+        Returns the shard's dImg partial [n,P,D] fp32 (None unless need_img)."""
+        dev = _require_cuda(txt_op, img_sh, arg_sh, w, dtxt)
+        Bt, D = txt_op.shape[0], txt_op.shape[2]
+        n = img_sh.shape[0]
+        assert w.is_contiguous() and w.dtype == torch.float32 and img_sh.is_contiguous() and arg_sh.is_contiguous()
+        assert dtxt is None or (dtxt.is_contiguous() and dtxt.dtype == torch.float32)
+        dimg = torch.empty((n, P, D), dtype=torch.float32, device=dev) if need_img else None
+        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        with torch.cuda.device(dev):
+            nws = int(self.lib.cxl_maxsim_bwd_workspace_bytes(Bt, n, T, P, D, dt)) if need_img else 0
+            ws = torch.empty(nws, dtype=torch.uint8, device=dev) if nws > 0 else None
+            check(self.lib.cxl_maxsim_bwd_shard(_ptr(txt_op), _ptr(img_sh), _ptr(arg_sh), _ptr(w), Bt, n, T, P, D, dt,
+                                                w.shape[1], k_off, _ptr(dtxt), 1 if accumulate_txt else 0, _ptr(dimg),
+                                                0, _ptr(ws), nws, _stream()), "cxl_maxsim_bwd_shard")
+        return dimg
+
+    def maxsim_bwd_dtxt_rows_shard(self, img_sh, arg_sh, w, k_off: int, Bt_total: int, m0: int, m_cnt: int, T: int,
+                                   P: int, prec: str, dtxt: torch.Tensor, accumulate_txt: bool):
+        """dTxt of texts m0..m0+m_cnt-1 against one shard of the images (shard-local img / argmax), into dtxt
+        [m_cnt,T,D] fp32 (overwritten or accumulated)."""
+        dev = _require_cuda(img_sh, arg_sh, w, dtxt)
+        D = img_sh.shape[2]
+        assert w.is_contiguous() and w.dtype == torch.float32 and w.shape[0] == Bt_total
+        assert dtxt.is_contiguous() and dtxt.dtype == torch.float32
+        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_maxsim_bwd_dtxt_rows_shard(_ptr(img_sh), _ptr(arg_sh), _ptr(w), Bt_total, m0, m_cnt,
+                                                          img_sh.shape[0], T, P, D, dt, w.shape[1], k_off, _ptr(dtxt),
+                                                          1 if accumulate_txt else 0, _stream()),
+                  "cxl_maxsim_bwd_dtxt_rows_shard")
+        return dtxt
 
     def maxsim_bwd_dtxt_rows(self, img_op, argmax, w, Bt_total: int, m0: int, m_cnt: int, T: int, P: int, prec: str,
                              generic: bool = False):

@@ -177,10 +177,59 @@ def _reduce_scatter_rows(x_all: torch.Tensor, world_size: int, group) -> torch.T
     return out
 
 
-def _dimg_all_max_bytes() -> int:
-    """Largest fp32 dImg partial over all gathered images the multi-GPU backward materialises in one piece
-    (CXL_DIMG_GATHER_MAX_GB, default 48); above it the images are processed one home rank at a time."""
-    return int(float(os.environ.get("CXL_DIMG_GATHER_MAX_GB", "48")) * (1 << 30))
+def _dimg_chunk_images(b: int, P: int, D: int) -> int:
+    """Images per dImg partial that goes home in one SUM-reduce (multi-GPU backward).  The fp32 partial of a whole
+    home-rank shard is 14.5 GB at cfg-5; CXL_DIMG_REDUCE_MB (default 4096) bounds it, two partials are in flight."""
+    limit = max(1, int(float(os.environ.get("CXL_DIMG_REDUCE_MB", "4096")) * (1 << 20)))
+    n_chunks = max(1, -(-(b * P * D * 4) // limit))
+    return -(-b // n_chunks)
+
+
+_COMM_STREAMS = {}
+
+
+def _comm_stream(dev: torch.device):
+    """Side stream for the shard broadcasts / dImg reductions, so they overlap K1 / K2 on the current stream."""
+    key = (dev.type, dev.index)
+    if key not in _COMM_STREAMS:
+        _COMM_STREAMS[key] = torch.cuda.Stream(device=dev)
+    return _COMM_STREAMS[key]
+
+
+def _global_rank(group, r: int) -> int:
+    return dist.get_global_rank(group, r) if group is not None else r
+
+
+def _gather_shards(x: torch.Tensor, world_size: int, rank: int, group):
+    """Every rank's `x` as SEPARATE tensors (shard r = rank r's x; this rank's own is `x` itself, no copy), fetched by
+    one broadcast per home rank on a side stream: K1 starts on the local shard at once and takes each remote shard as
+    it lands (ready[r] is the CUDA event to wait for, None when nothing is pending), and the backward can free the
+    shards one by one.  Replaces all_gather of the reference's gather_features (loss.py:70-86) for the token operand."""
+    shards = [x if r == rank else torch.empty_like(x) for r in range(world_size)]
+    ready = [None] * world_size
+    if world_size == 1:
+        return shards, ready
+    if x.is_cuda:
+        main, comm = torch.cuda.current_stream(x.device), _comm_stream(x.device)
+        comm.wait_stream(main)                       # the local operand (and the fresh buffers' memory) are ready
+        with torch.cuda.stream(comm):
+            for r in range(world_size):
+                dist.broadcast(shards[r], src=_global_rank(group, r), group=group)
+                if r != rank:
+                    ready[r] = torch.cuda.Event()
+                    ready[r].record(comm)
+        x.record_stream(comm)
+    else:
+        for r in range(world_size):
+            dist.broadcast(shards[r], src=_global_rank(group, r), group=group)
+    return shards, ready
+
+
+class _FwdState:
+    """What the fused forward keeps for its backward.  Held on the autograd ctx as a plain object (not through
+    save_for_backward) because the backward releases the image shards and their argmax one home rank at a time."""
+    __slots__ = ("txt_op", "shards", "args", "cnt", "S", "G", "g_txt", "g_img", "scale", "rl_g", "cl_g", "rl_t",
+                 "cl_t", "consumed")
 
 
 def _round_like_gemm_input(x: torch.Tensor, prec: str) -> torch.Tensor:
@@ -214,15 +263,29 @@ class _ColClipLossFn(torch.autograd.Function):
         row0 = rank * b
         dev = token_image_features.device
 
-        # K4 (forward half): all-gather of the packed bf16 image tokens + global image features
-        txt_op = k.prepare(token_text_features, T, prec)
-        img_op = _all_gather_cat(k.prepare(token_image_features, k.img_row_stride(P, prec), prec), W, group)
+        # global features first (small collectives), then the token operand: one broadcast per home rank on a side
+        # stream (K4, forward half) -- K1 runs on the local shard while the remote ones arrive
         g_txt = _round_like_gemm_input(text_features, prec)
         g_img = _all_gather_cat(_round_like_gemm_input(image_features, prec), W, group)
+        txt_op = k.prepare(token_text_features, T, prec)
+        shards, ready = _gather_shards(k.prepare(token_image_features, k.img_row_stride(P, prec), prec), W, rank, group)
 
-        # K1: token-level scores of this rank's texts against all images
+        # K1: token-level scores of this rank's texts against all images, one home rank's shard at a time
         need_bwd = bool(cfg.get("need_bwd", True))
-        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, MASKED, need_bwd)
+        args = [None] * W
+        if W == 1:
+            S, cnt, args[0] = k.maxsim_fwd(txt_op, shards[0], T, P, prec, MASKED, need_bwd)
+        else:
+            S = torch.empty((b, B), dtype=torch.float32, device=dev)
+            cnt = torch.empty((b, B), dtype=torch.float32, device=dev)
+            for i in range(W):
+                r = (rank + i) % W                       # own shard first: nothing to wait for
+                if ready[r] is not None:
+                    torch.cuda.current_stream(dev).wait_event(ready[r])
+                S_r, cnt_r, args[r] = k.maxsim_fwd(txt_op, shards[r], T, P, prec, MASKED, need_bwd)
+                S[:, r * b:(r + 1) * b] = S_r
+                cnt[:, r * b:(r + 1) * b] = cnt_r
+                del S_r, cnt_r
         # global CLIP scores (plain library GEMM, fp32 accumulate) -- SURVEY 8 f-1
         G = g_txt @ g_img.T
 
@@ -241,8 +304,12 @@ class _ColClipLossFn(torch.autograd.Function):
         total = alpha * loss_g + (1.0 - alpha) * loss_t
 
         if need_bwd:
-            ctx.save_for_backward(txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale,
-                                  stats[0][0], stats[0][1], stats[1][0], stats[1][1])
+            st = _FwdState()
+            st.txt_op, st.shards, st.args, st.cnt, st.S, st.G = txt_op, shards, args, cnt, S, G
+            st.g_txt, st.g_img, st.scale = g_txt, g_img, scale
+            st.rl_g, st.cl_g, st.rl_t, st.cl_t = stats[0][0], stats[0][1], stats[1][0], stats[1][1]
+            st.consumed = False
+            ctx.state = st
         ctx.cfg = cfg
         ctx.meta = (T, P, b, row0, image_features.dtype, text_features.dtype, token_image_features.dtype,
                     token_text_features.dtype, logit_scale.dtype, logit_scale.shape)
@@ -251,97 +318,161 @@ class _ColClipLossFn(torch.autograd.Function):
     @staticmethod
     @once_differentiable
     def backward(ctx, g):
-        return _colclip_backward(ctx.saved_tensors, ctx.cfg, ctx.meta, g, ctx.needs_input_grad) + (None,)
+        # consume=True: w / dG overwrite S / G and every shard is released as soon as K2 is done with it
+        return _colclip_backward(ctx.state, ctx.cfg, ctx.meta, g, ctx.needs_input_grad, consume=True) + (None,)
 
 
-def _colclip_backward(saved, cfg, meta, g, need):
-    """Gradients of losses[3] w.r.t. (image, text, token image, token text features, logit_scale) from the tensors the
-    forward saved.  cfg["grad_rows"] restricts the token gradients to one slice of the local batch (zeros elsewhere, or
-    just the slices of all four feature gradients when cfg["slice_out"] is set)."""
+def _send_home(part, home, lo, hi, out_ref, cfg, shape, dtype, mult, inflight):
+    """SUM-reduce one dImg partial (images lo..hi-1 of home rank `home`'s shard) to its home rank, on the side stream
+    so that K2 goes on with the next images; the home rank casts the sum into rows lo..hi-1 of its output."""
+    W, rank, group = cfg["world_size"], cfg["rank"], cfg.get("group")
+    if part.is_cuda:
+        main, comm = torch.cuda.current_stream(part.device), _comm_stream(part.device)
+        comm.wait_stream(main)
+        with torch.cuda.stream(comm):
+            dist.reduce(part, dst=_global_rank(group, home), group=group)
+            if rank == home:
+                if out_ref[0] is None:
+                    out_ref[0] = torch.empty(shape, dtype=dtype, device=part.device)
+                out_ref[0][lo:hi].copy_(part if mult == 1.0 else part * mult)
+            ev = torch.cuda.Event()
+            ev.record(comm)
+        part.record_stream(comm)
+        inflight.append(ev)
+        if len(inflight) > 1:                       # at most two partials alive: wait for the one before the last
+            main.wait_event(inflight.pop(0))
+    else:
+        dist.reduce(part, dst=_global_rank(group, home), group=group)
+        if rank == home:
+            if out_ref[0] is None:
+                out_ref[0] = torch.empty(shape, dtype=dtype)
+            out_ref[0][lo:hi].copy_(part if mult == 1.0 else part * mult)
+
+
+def _colclip_backward(st, cfg, meta, g, need, consume=False):
+    """Gradients of losses[3] w.r.t. (image, text, token image, token text features, logit_scale) from the forward's
+    state.  cfg["grad_rows"] restricts the token gradients to one slice of the local batch (zeros elsewhere, or just
+    the slices of all four feature gradients when cfg["slice_out"] is set).  consume: this is the only backward of
+    that forward -- the pair weights / dG are written over S / G and shards are freed as K2 finishes them."""
     k = cfg["kernels"]
-    W, group = cfg["world_size"], cfg.get("group")
+    W, rank, group = cfg["world_size"], cfg["rank"], cfg.get("group")
     alpha, prec = float(cfg["alpha"]), cfg["prec"]
     T, P, b, row0, dt_img, dt_txt, dt_timg, dt_ttxt, dt_ls, ls_shape = meta
-    (txt_op, img_op, argmax, cnt, S, G, g_txt, g_img, scale, rl_g, cl_g, rl_t, cl_t) = saved
+    if st.consumed:
+        raise RuntimeError("colxlip_b200: this ColClipLoss forward was already back-propagated (its buffers were "
+                           "reused in place); retain_graph / double backward are not supported by the fused loss")
+    txt_op, cnt, S, G, scale = st.txt_op, st.cnt, st.S, st.G, st.scale
+    D = txt_op.shape[2]
+    dev = txt_op.device
     g = g.float()
     coef_g = (g[0] + alpha * g[2]).reshape(1).contiguous()
     coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
 
     # K3 gradient pass (also yields d logit_scale partials of this rank's rows)
-    w, dscale_t = k.infonce_grad(S, scale, coef_t, row0, rl_t, cl_t, cnt=cnt)   # pair weights dL/dS / cnt
-    dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, rl_g, cl_g)
+    w, dscale_t = k.infonce_grad(S, scale, coef_t, row0, st.rl_t, st.cl_t, cnt=cnt, out=S if consume else None)
+    dG, dscale_g = k.infonce_grad(G, scale, coef_g, row0, st.rl_g, st.cl_g, out=G if consume else None)
+    if consume:
+        st.consumed = True
+        st.S = st.G = st.cnt = None
+    del cnt, S, G
     dscale = dscale_t + dscale_g
     if W > 1:
         dist.all_reduce(dscale, group=group)
 
-    d_txt = dG @ g_img if need[1] else None
-    d_img_all = dG.T @ g_txt if need[0] else None
     mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
-    rows = cfg.get("grad_rows")
-    if rows is None and W > 1 and need[2] and img_op.shape[0] * P * img_op.shape[2] * 4 > _dimg_all_max_bytes():
-        # The fp32 dImg partial over ALL gathered images would not fit next to the argmax (cfg-5: 116 GB per rank):
-        # go through the images one home rank at a time -- K2 on the shard of rank r (k_off / n_img), SUM-reduce to r.
-        dtxt_tok = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=True, need_img=False)[0] \
-            if need[3] else None
-        dimg_tok = None
-        for r in range(W):
-            part = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
-                                k_off=r * b, n_img=b)[1]
-            dist.reduce(part, dst=(dist.get_global_rank(group, r) if group is not None else r), group=group)
-            if r == cfg["rank"]:
-                dimg_tok = part
-            del part
-    elif rows is None:
-        # K2: token gradients from the saved argmax
-        dtxt_tok, dimg_tok_all = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec,
-                                              need_txt=need[3], need_img=need[2])
-        # K4 (backward half): image-side partials go home by SUM reduce-scatter; gather_with_grad=True
-        # reproduces the reference's x world_size (every rank back-propagates the same full loss).
-        dimg_tok = _reduce_scatter_rows(dimg_tok_all, W, group) if need[2] else None
-    else:
-        # gradient-accumulation call (train.py:166-183): only samples lo..hi-1 of every rank's batch carry
-        # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items; the rest stays zero
-        lo, hi = rows
-        n = hi - lo
-        dtxt_tok = dimg_tok = None
-        slice_out = bool(cfg.get("slice_out"))
-        if need[3]:
-            part = k.maxsim_bwd_dtxt_rows(img_op, argmax, w, b, lo, n, T, P, prec)
-            if slice_out:
-                dtxt_tok = part
-            else:
-                dtxt_tok = torch.zeros((b, T, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
-                dtxt_tok[lo:hi] = part
-        if need[2]:
-            parts = [k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=False, need_img=True,
-                                  k_off=r * b + lo, n_img=n)[1] for r in range(W)]
-            home = _reduce_scatter_rows(torch.cat(parts) if W > 1 else parts[0], W, group)
-            if slice_out:
-                dimg_tok = home
-            else:
-                dimg_tok = torch.zeros((b, P, txt_op.shape[2]), dtype=torch.float32, device=txt_op.device)
-                dimg_tok[lo:hi] = home
-    d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
-    if rows is not None and cfg.get("slice_out"):
-        d_img = d_img[rows[0]:rows[1]] if d_img is not None else None
-        d_txt = d_txt[rows[0]:rows[1]] if d_txt is not None else None
+    d_txt = dG @ st.g_img if need[1] else None
+    d_img = _reduce_scatter_rows(dG.T @ st.g_txt, W, group) if need[0] else None
+    del dG
 
-    def fin(x, dt):
+    # K2: token gradients from the saved argmax, one home rank's shard at a time in rank order (the order fixes the
+    # chain of fp32 additions of dTxt: same bits as one call over all images).  K4 (backward half): each dImg
+    # partial is SUM-reduced to its home rank while K2 works on the next one; gather_with_grad=True reproduces the
+    # reference's x world_size (every rank back-propagates the same full loss).
+    rows = cfg.get("grad_rows")
+    slice_out = bool(cfg.get("slice_out")) and rows is not None
+    lo_t, hi_t = rows if rows is not None else (0, b)
+    n_t = hi_t - lo_t
+    dtxt_tok = None
+    if need[3]:
+        dtxt_tok = torch.empty((n_t, T, D), dtype=torch.float32, device=dev)
+    out_ref, inflight = [None], []
+    chunk = _dimg_chunk_images(n_t, P, D) if W > 1 else n_t
+    for r in range(W):
+        img_sh, arg_sh = st.shards[r], st.args[r]
+        if rows is None:
+            first = True
+            for lo in range(0, b, chunk):
+                hi = min(b, lo + chunk)
+                part = k.maxsim_bwd_shard(txt_op, img_sh[lo:hi], k.argmax_images(arg_sh, lo, hi), w, r * b + lo, T, P,
+                                          prec, dtxt=dtxt_tok, accumulate_txt=not (r == 0 and first), need_img=need[2])
+                first = False
+                if need[2]:
+                    if W == 1:
+                        out_ref[0] = part if (lo == 0 and hi == b) else _place(out_ref, part, lo, hi, (b, P, D))
+                    else:
+                        _send_home(part, r, lo, hi, out_ref, cfg, (b, P, D), dt_timg, mult, inflight)
+                del part
+        else:
+            # gradient-accumulation call (train.py:166-183): only samples lo_t..hi_t-1 of every rank's batch carry
+            # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items
+            if need[3]:
+                k.maxsim_bwd_dtxt_rows_shard(img_sh, arg_sh, w, r * b, b, lo_t, n_t, T, P, prec, dtxt_tok, r > 0)
+            if need[2]:
+                for lo in range(lo_t, hi_t, chunk):
+                    hi = min(hi_t, lo + chunk)
+                    part = k.maxsim_bwd_shard(txt_op, img_sh[lo:hi], k.argmax_images(arg_sh, lo, hi), w, r * b + lo,
+                                              T, P, prec, need_img=True)
+                    if W == 1:
+                        out_ref[0] = part if (lo == lo_t and hi == hi_t) else _place(out_ref, part, lo - lo_t, hi - lo_t,
+                                                                                     (n_t, P, D))
+                    else:
+                        _send_home(part, r, lo - lo_t, hi - lo_t, out_ref, cfg, (n_t, P, D), dt_timg, mult, inflight)
+                    del part
+        del img_sh, arg_sh
+        if consume and W > 1:
+            st.shards[r] = None                     # this rank is done with home rank r's images: 1/W of the gathered
+            st.args[r] = None                       # operand and of the argmax go back to the allocator now
+    if inflight:
+        torch.cuda.current_stream(dev).wait_stream(_comm_stream(dev))
+    dimg_tok = out_ref[0] if need[2] else None
+    if consume:
+        st.shards = st.args = None
+
+    if rows is not None and not slice_out:          # zeros outside the slice (torch.cat's backward drops them anyway)
+        if dtxt_tok is not None:
+            full = torch.zeros((b, T, D), dtype=torch.float32, device=dev)
+            full[lo_t:hi_t] = dtxt_tok
+            dtxt_tok = full
+        if dimg_tok is not None:
+            full = torch.zeros((b, P, D), dtype=dimg_tok.dtype, device=dev)
+            full[lo_t:hi_t] = dimg_tok
+            dimg_tok = full
+    if slice_out:
+        d_img = d_img[lo_t:hi_t] if d_img is not None else None
+        d_txt = d_txt[lo_t:hi_t] if d_txt is not None else None
+
+    def fin(x, dt, scaled=False):
         if x is None:
             return None
-        if mult != 1.0:
+        if mult != 1.0 and not scaled:
             x = x * mult
         return x.to(dt)
 
     d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[4] else None
-    return fin(d_img, dt_img), fin(d_txt, dt_txt), fin(dimg_tok, dt_timg), fin(dtxt_tok, dt_ttxt), d_ls
+    return (fin(d_img, dt_img), fin(d_txt, dt_txt), fin(dimg_tok, dt_timg, scaled=W > 1), fin(dtxt_tok, dt_ttxt), d_ls)
+
+
+def _place(out_ref, part, lo, hi, shape):
+    """single-GPU chunked dImg (not used by the default plan: one chunk): collect the chunks in one fp32 buffer"""
+    if out_ref[0] is None or out_ref[0].shape != tuple(shape):
+        out_ref[0] = torch.empty(shape, dtype=torch.float32, device=part.device)
+    out_ref[0][lo:hi] = part
+    return out_ref[0]
 
 
 class _SavedForward:
-    """Stand-in for an autograd ctx: lets `_ColClipLossFn._forward` run outside autograd and keeps what it saves."""
-
-    def save_for_backward(self, *tensors):
-        self.saved_tensors = tensors
+    """Stand-in for an autograd ctx: lets `_ColClipLossFn._forward` run outside autograd and keeps its state."""
+    state = None
 
 
 class _AccumSliceFn(torch.autograd.Function):
@@ -361,7 +492,7 @@ class _AccumSliceFn(torch.autograd.Function):
         st = ctx.state
         cfg = dict(st.fwd.cfg, grad_rows=ctx.rows, slice_out=True)
         meta = st.fwd.meta[:4] + ctx.dtypes
-        return _colclip_backward(st.fwd.saved_tensors, cfg, meta, g, ctx.needs_input_grad) + (None, None, None)
+        return _colclip_backward(st.fwd.state, cfg, meta, g, ctx.needs_input_grad, consume=False) + (None, None, None)
 
 
 class ColClipAccumulation:
@@ -395,7 +526,7 @@ class ColClipAccumulation:
             T, P = self.fwd.meta[0], self.fwd.meta[1]
             k, prec = self.fwd.cfg["kernels"], self.fwd.cfg["prec"]
             live = k.prepare(token_text_features, T, prec)
-            if not torch.equal(live, self.fwd.saved_tensors[0][lo:hi]):
+            if not torch.equal(live, self.fwd.state.txt_op[lo:hi]):
                 raise RuntimeError("live text-token features differ from the cached ones: the model is not "
                                    "deterministic between passes; use ColClipLoss.forward(grad_rows=...) instead")
         losses = _AccumSliceFn.apply(*feats, logit_scale, self, lo, hi)

@@ -130,6 +130,26 @@ int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w
                              int force_generic, void* stream);
 
 /*
+ * The same backward for ONE SHARD of the images with shard-local operands -- the multi-GPU pipeline (reference
+ * loss.py:48-92 + autograd of loss.py:34-44): each rank scores its texts against one home rank's images at a time,
+ * keeps that shard's operand and argmax as separate buffers (so they can be freed shard by shard: at ViT-L/14@336,
+ * B = 65536 on 8 GPUs the gathered operand + argmax are 131 GiB per rank) and sends the dImg partial home.
+ *   img    [Bi, p_stride, D]   the shard's image operand          argmax [Bi][cxl_argmax_ld(Bt,T)]  the shard's own
+ *   w      [Bt, ld_pairs]      pair weights over ALL images; the shard is columns [k_off, k_off + Bi)
+ *   dtxt   [Bt,T,D] or NULL; accumulate_txt != 0: dtxt += this shard's sum.  Shards taken in ascending image order
+ *          continue the same chain of additions, so the result has the bits of one call over all images.
+ *   dimg   [Bi,P,D] or NULL (the shard's partial), accumulate_img as above.
+ * A sub-range [lo, lo+n) of a shard is the same call with img / argmax / dimg advanced by lo images and k_off + lo.
+ */
+int cxl_maxsim_bwd_shard(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
+                         int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, int accumulate_txt,
+                         float* dimg, int accumulate_img, void* ws, size_t ws_bytes, void* stream);
+/* cxl_maxsim_bwd_dtxt_rows for one shard with shard-local img / argmax (see above), optionally accumulating. */
+int cxl_maxsim_bwd_dtxt_rows_shard(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
+                                   int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
+                                   int accumulate_txt, void* stream);
+
+/*
  * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,
  * columns = all B images; labels are the diagonal).  Replaces `logit_scale *` and the
  * F.cross_entropy pairs of loss.py:252-263, 285-293.

@@ -18,7 +18,10 @@ import torch.multiprocessing as mp
 
 HERE = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, os.path.join(HERE, "..", ".."))
-WORLD, B_LOC, P, T, D, SEED, SCALE, ALPHA = 2, 4, 6, 5, 16, 9, 12.0, 0.4
+# python tests/golden/make_golden_dist.py [WORLD]   (2 -> dist_w2.npz, the historical file; 4 / 8 -> dist_w4 / dist_w8.npz)
+WORLD = int(sys.argv[1]) if len(sys.argv) > 1 and __name__ == "__main__" else int(os.environ.get("CXL_GOLDEN_WORLD", "2"))
+B_LOC = {2: 4, 4: 3, 8: 2}.get(WORLD, 2)
+P, T, D, SEED, SCALE, ALPHA = 6, 5, 16, 9 + (WORLD if WORLD != 2 else 0), 12.0, 0.4
 
 
 def _worker(rank, port, q):
@@ -104,6 +107,7 @@ def main():
     s.bind(("127.0.0.1", 0))
     port = s.getsockname()[1]
     s.close()
+    os.environ["CXL_GOLDEN_WORLD"] = str(WORLD)          # spawned workers re-import this module
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     procs = [ctx.Process(target=_worker, args=(r, port, q)) for r in range(WORLD)]
@@ -117,7 +121,7 @@ def main():
         assert p.exitcode == 0
     from oracle.colxlip_oracle import synth_inputs
     feats = synth_inputs(B_LOC * WORLD, P, T, D, seed=SEED, pad_text=True)
-    np.savez_compressed(os.path.join(HERE, "dist_w2.npz"), world=WORLD, b=B_LOC, P=P, T=T, D=D, seed=SEED,
+    np.savez_compressed(os.path.join(HERE, f"dist_w{WORLD}.npz"), world=WORLD, b=B_LOC, P=P, T=T, D=D, seed=SEED,
                         scale=SCALE, alpha=ALPHA, image_features=feats[0].numpy(), text_features=feats[1].numpy(),
                         token_image_features=feats[2].numpy(), token_text_features=feats[3].numpy(), **merged)
     for k in sorted(merged):

@@ -33,6 +33,10 @@ class TorchRefKernels:
             S = mx.mean(dim=2)
         return S, cnt, (arg if save_argmax else None)
 
+    @staticmethod
+    def argmax_images(argmax, lo, hi):
+        return argmax[:, lo:hi]                                  # the stand-in keeps the argmax text-major [Bt,Bi,T]
+
     def pair_weights(self, dS, cnt, T, mean_mode):
         return dS.float() / ((cnt + 1e-8) if mean_mode == MASKED else float(T))
 
@@ -55,6 +59,32 @@ class TorchRefKernels:
                 contrib = (w[:, k, None, None] * txt_op).reshape(Bt * T, D)
                 dimg[k].index_add_(0, arg[:, k].reshape(-1), contrib)
         return dtxt, dimg
+
+    def maxsim_bwd_shard(self, txt_op, img_sh, arg_sh, w, k_off, T, P, prec, dtxt=None, accumulate_txt=False,
+                         need_img=True):
+        """arg_sh: the shard's argmax [Bt, n, T] (what maxsim_fwd(txt_op, img_sh) returned)."""
+        Bt, _, D = txt_op.shape
+        n = img_sh.shape[0]
+        ws = w[:, k_off:k_off + n]
+        if dtxt is not None:
+            if not accumulate_txt:
+                dtxt.zero_()
+            for k in range(n):
+                dtxt += ws[:, k, None, None] * img_sh[k][arg_sh[:, k]]
+        dimg = None
+        if need_img:
+            dimg = torch.zeros(n, P, D)
+            for k in range(n):
+                contrib = (ws[:, k, None, None] * txt_op).reshape(Bt * T, D)
+                dimg[k].index_add_(0, arg_sh[:, k].reshape(-1), contrib)
+        return dimg
+
+    def maxsim_bwd_dtxt_rows_shard(self, img_sh, arg_sh, w, k_off, Bt_total, m0, m_cnt, T, P, prec, dtxt, accumulate_txt):
+        if not accumulate_txt:
+            dtxt.zero_()
+        for k in range(img_sh.shape[0]):
+            dtxt += w[m0:m0 + m_cnt, k_off + k, None, None] * img_sh[k][arg_sh[m0:m0 + m_cnt, k]]
+        return dtxt
 
     def maxsim_bwd_dtxt_rows(self, img_op, argmax, w, Bt_total, m0, m_cnt, T, P, prec, generic=False):
         D = img_op.shape[2]

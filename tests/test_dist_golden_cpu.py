@@ -16,6 +16,7 @@ from oracle import colxlip_oracle as O
 from tests.ref_kernels import TorchRefKernels
 
 GOLDEN = os.path.join(os.path.dirname(__file__), "golden", "dist_w2.npz")
+GOLDEN_W = {w: os.path.join(os.path.dirname(__file__), "golden", f"dist_w{w}.npz") for w in (2, 4, 8)}
 NAMES = ("image_features", "text_features", "token_image_features", "token_text_features")
 
 
@@ -25,9 +26,10 @@ def _close(a, ref, rel=1e-5):
 
 
 # ---- the oracle's rules vs the reference's multi-rank run ---------------------------------------------
+@pytest.mark.parametrize("world", [2, 4, 8])
 @pytest.mark.parametrize("gwg", [0, 1])
-def test_oracle_colclip_scaling_rule_matches_reference_ranks(gwg):
-    z = np.load(GOLDEN)
+def test_oracle_colclip_scaling_rule_matches_reference_ranks(gwg, world):
+    z = np.load(GOLDEN_W[world])
     W, b = int(z["world"]), int(z["b"])
     feats = [torch.from_numpy(z[n]) for n in NAMES]
     losses, grads = O.loss_and_grads(*feats, float(z["scale"]), float(z["alpha"]))
@@ -86,11 +88,12 @@ def _free_port():
 def _worker(rank, world, port, q):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
+    os.environ["CXL_DIMG_REDUCE_MB"] = "0.0005"        # dImg partials go home in chunks of one or two images
     dist.init_process_group("gloo", rank=rank, world_size=world)
     torch.set_num_threads(1)
     out = {}
     try:
-        z = np.load(GOLDEN)
+        z = np.load(GOLDEN_W[world])
         b, scale, alpha = int(z["b"]), float(z["scale"]), float(z["alpha"])
         sl = slice(rank * b, (rank + 1) * b)
         feats = [torch.from_numpy(z[n])[sl] for n in NAMES]
@@ -177,9 +180,10 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
-def test_world2_gloo_matches_reference_ranks():
-    z = np.load(GOLDEN)
-    world = int(z["world"])
+@pytest.mark.parametrize("world", [2, 4])
+def test_gloo_ranks_match_reference_ranks(world):
+    z = np.load(GOLDEN_W[world])
+    assert int(z["world"]) == world
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
