@@ -15,6 +15,7 @@ LIB_PATH = os.path.join(_PKG, "libcolxlip_b200.so")
 
 CXL_DTYPE_F32 = 0
 CXL_DTYPE_BF16 = 1
+CXL_DTYPE_F16 = 2
 CXL_MEAN_MASKED = 0
 CXL_MEAN_PLAIN = 1
 
@@ -41,9 +42,12 @@ SYMBOLS = {
     "cxl_maxsim_bwd_dtxt_rows": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                          c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
     "cxl_maxsim_bwd_shard": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
-                                     c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_size_t, c_void_p]),
+                                     c_int, c_int, c_void_p, c_int, c_void_p, c_int, c_void_p, c_void_p, c_size_t,
+                                     c_void_p]),
     "cxl_maxsim_bwd_dtxt_rows_shard": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
-                                               c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p]),
+                                               c_int, c_int, c_int, c_int, c_void_p, c_int, c_void_p, c_void_p]),
+    "cxl_pack_operand": (c_int, [c_void_p, c_int, c_longlong, c_longlong, c_int, c_int, c_int, c_int, c_void_p, c_int,
+                                 c_void_p]),
     "cxl_maxsim_bwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int, c_int, c_int]),
     "cxl_maxsim_bwd_generic": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int,
                                        c_int, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),

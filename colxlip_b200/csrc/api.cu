@@ -30,14 +30,14 @@ int num_sms() {
 
 int img_row_stride(int P);
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid,
+                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, int f16,
                   cudaStream_t stream);
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
                    float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
                float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, int force_generic, void* ws,
-               size_t ws_bytes, cudaStream_t stream);
+               size_t ws_bytes, const float* w_scale, cudaStream_t stream);
 size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D);
 int pair_weights(const float* dS, const float* cnt, const float* gscale, int mean_mode, int T, long long n, float* w,
                  cudaStream_t stream);
@@ -49,6 +49,8 @@ int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, 
                  cudaStream_t stream);
 int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
               int D, void* dst, cudaStream_t stream);
+int pack_operand(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n,
+                 int n_pad, int D, void* dst, int dst_dtype, cudaStream_t stream);
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                    const int* target, int* rank_out, cudaStream_t stream);
 
@@ -105,6 +107,15 @@ int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, lon
                    static_cast<cudaStream_t>(stream));
 }
 
+int cxl_pack_operand(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride, int items,
+                     int n, int n_pad, int D, void* dst, int dst_dtype, void* stream) {
+  if (src == nullptr || dst == nullptr) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return pack_operand(src, src_dtype, src_item_stride, src_row_stride, items, n, n_pad, D, dst, dst_dtype,
+                      static_cast<cudaStream_t>(stream));
+}
+
 int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
                    float* S, float* cnt, void* argmax, void* stream) {
   if (txt == nullptr || img == nullptr || S == nullptr) return CXL_ERR_INVALID_ARG;
@@ -116,8 +127,9 @@ int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int 
   if (rc != CXL_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long ld_arg = cxl_argmax_ld(Bt, T);
-  if (dtype == CXL_DTYPE_BF16)
-    return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0, st);
+  if (dtype == CXL_DTYPE_BF16 || dtype == CXL_DTYPE_F16)
+    return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0,
+                         dtype == CXL_DTYPE_F16, st);
   if (dtype == CXL_DTYPE_F32)
     return maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
                           cnt, argmax, ld_arg, st);
@@ -138,12 +150,12 @@ static int bwd_entry(const void* txt, const void* img, const void* argmax, const
                      int force_generic, void* ws, size_t ws_bytes, void* stream) {
   if (txt == nullptr || img == nullptr || argmax == nullptr || w == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
-  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32 && dtype != CXL_DTYPE_F16) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const int p_stride = dtype != CXL_DTYPE_F32 ? img_row_stride(P) : P;
   return maxsim_bwd(txt, img, argmax, cxl_argmax_ld(Bt, T), 0, w, Bt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off,
-                    dtxt, 0, dimg, accumulate_img, force_generic, ws, ws_bytes, static_cast<cudaStream_t>(stream));
+                    dtxt, 0, dimg, accumulate_img, force_generic, ws, ws_bytes, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
@@ -152,14 +164,14 @@ int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w
   if (img == nullptr || argmax == nullptr || w == nullptr || dtxt == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt_total <= 0 || m0 < 0 || m_cnt <= 0 || m0 + m_cnt > Bt_total) return CXL_ERR_INVALID_ARG;
   if (Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
-  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32 && dtype != CXL_DTYPE_F16) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const int p_stride = dtype != CXL_DTYPE_F32 ? img_row_stride(P) : P;
   // dTxt never reads the text operand; `img` stands in for the (unused) txt pointer of the shared dispatcher
   return maxsim_bwd(img, img, argmax, cxl_argmax_ld(Bt_total, T), static_cast<long long>(m0) * T,
                     w + static_cast<size_t>(m0) * ld_pairs, m_cnt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
-                    0, nullptr, 0, force_generic, nullptr, 0, static_cast<cudaStream_t>(stream));
+                    0, nullptr, 0, force_generic, nullptr, 0, nullptr, static_cast<cudaStream_t>(stream));
 }
 
 // Shard-local operands: `argmax` is the shard's own buffer; the kernels index argmax rows and w columns with the same
@@ -171,33 +183,34 @@ static const void* shard_argmax_base(const void* argmax, long long ld_arg, int P
 
 int cxl_maxsim_bwd_shard(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
                          int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, int accumulate_txt,
-                         float* dimg, int accumulate_img, void* ws, size_t ws_bytes, void* stream) {
+                         float* dimg, int accumulate_img, const float* w_scale_dev, void* ws, size_t ws_bytes,
+                         void* stream) {
   if (txt == nullptr || img == nullptr || argmax == nullptr || w == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0 || k_off < 0) return CXL_ERR_INVALID_ARG;
-  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32 && dtype != CXL_DTYPE_F16) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const int p_stride = dtype != CXL_DTYPE_F32 ? img_row_stride(P) : P;
   const long long ld_arg = cxl_argmax_ld(Bt, T);
   return maxsim_bwd(txt, img, shard_argmax_base(argmax, ld_arg, P, k_off), ld_arg, 0, w, Bt, Bi, T, P, D, dtype,
-                    p_stride, ld_pairs, k_off, dtxt, accumulate_txt, dimg, accumulate_img, 0, ws, ws_bytes,
+                    p_stride, ld_pairs, k_off, dtxt, accumulate_txt, dimg, accumulate_img, 0, ws, ws_bytes, w_scale_dev,
                     static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd_dtxt_rows_shard(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
                                    int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
-                                   int accumulate_txt, void* stream) {
+                                   int accumulate_txt, const float* w_scale_dev, void* stream) {
   if (img == nullptr || argmax == nullptr || w == nullptr || dtxt == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt_total <= 0 || m0 < 0 || m_cnt <= 0 || m0 + m_cnt > Bt_total || k_off < 0) return CXL_ERR_INVALID_ARG;
   if (Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
-  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F32 && dtype != CXL_DTYPE_F16) return CXL_ERR_INVALID_ARG;
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
-  const int p_stride = dtype == CXL_DTYPE_BF16 ? img_row_stride(P) : P;
+  const int p_stride = dtype != CXL_DTYPE_F32 ? img_row_stride(P) : P;
   const long long ld_arg = cxl_argmax_ld(Bt_total, T);
   return maxsim_bwd(img, img, shard_argmax_base(argmax, ld_arg, P, k_off), ld_arg, static_cast<long long>(m0) * T,
                     w + static_cast<size_t>(m0) * ld_pairs, m_cnt, Bi, T, P, D, dtype, p_stride, ld_pairs, k_off, dtxt,
-                    accumulate_txt, nullptr, 0, 0, nullptr, 0, static_cast<cudaStream_t>(stream));
+                    accumulate_txt, nullptr, 0, 0, nullptr, 0, w_scale_dev, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T, int P,
@@ -208,7 +221,7 @@ int cxl_maxsim_bwd(const void* txt, const void* img, const void* argmax, const f
 }
 
 size_t cxl_maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D, int dtype) {
-  if (dtype != CXL_DTYPE_BF16 || Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return 0;
+  if ((dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F16) || Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return 0;
   return maxsim_bwd_workspace_bytes(Bt, Bi, T, P, D);
 }
 
@@ -279,7 +292,7 @@ int cxl_debug_tile(const void* txt_bf16, const void* img_bf16, int rowsA, int ro
   CXL_CUDA_CHECK(cudaMallocAsync(&scratch, 2 * sizeof(float), st));
   // one "text" of rowsA tokens against one "image" of rowsB patches
   rc = maxsim_fwd_tc(txt_bf16, img_bf16, 1, 1, rowsA, rowsB, D, CXL_MEAN_PLAIN, scratch, scratch + 1, nullptr, 0, out, 0,
-                     0, st);
+                     0, 0, st);
   cudaFreeAsync(scratch, st);
   return rc;
 }
@@ -291,7 +304,7 @@ int cxl_maxsim_fwd_tc_ex(const void* txt, const void* img, int Bt, int Bi, int T
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, cxl_argmax_ld(Bt, T), nullptr,
-                       force_stream_a, force_grid, static_cast<cudaStream_t>(stream));
+                       force_stream_a, force_grid, 0, static_cast<cudaStream_t>(stream));
 }
 
 // Test hook: backward through the generic (non-streaming) kernels regardless of shape.

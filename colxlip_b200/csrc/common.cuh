@@ -4,6 +4,7 @@
 
 #include <cuda.h>
 #include <cuda_bf16.h>
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -131,12 +132,12 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr) {
   d |= static_cast<uint64_t>(2) << 61;             // SWIZZLE_128B
   return d;
 }
-// kind::f16 instruction descriptor: D=f32, A=B=bf16, both K-major, shape M x N.
-__host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N) {
+// kind::f16 instruction descriptor: D=f32, A=B=bf16 (or fp16 when f16 != 0), both K-major, shape M x N.
+__host__ __device__ inline uint32_t umma_idesc_bf16(int M, int N, int f16 = 0) {
   uint32_t d = 0;
   d |= 1u << 4;                            // c_format  = F32
-  d |= 1u << 7;                            // a_format  = BF16
-  d |= 1u << 10;                           // b_format  = BF16
+  d |= (f16 ? 0u : 1u) << 7;               // a_format: 0 = F16, 1 = BF16
+  d |= (f16 ? 0u : 1u) << 10;              // b_format
   d |= static_cast<uint32_t>(N >> 3) << 17;  // n_dim
   d |= static_cast<uint32_t>(M >> 4) << 24;  // m_dim
   return d;

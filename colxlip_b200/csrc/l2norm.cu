@@ -42,6 +42,28 @@ template <> struct Row8<__nv_bfloat16> {
   }
 };
 
+template <> struct Row8<__half> {
+  __device__ static void load(const __half* p, float (&o)[8]) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      o[2 * i] = f.x;
+      o[2 * i + 1] = f.y;
+    }
+  }
+  __device__ static void store(__half* p, const float (&v)[8]) {
+    uint32_t w[4];
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const __half2 h = __floats2half2_rn(v[2 * i], v[2 * i + 1]);
+      w[i] = *reinterpret_cast<const uint32_t*>(&h);
+    }
+    *reinterpret_cast<uint4*>(p) = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+};
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
@@ -134,6 +156,9 @@ int l2norm_fwd(const void* x, int x_dtype, long long rows, int D, void* y, int y
   else if (x_dtype == CXL_DTYPE_F32 && y_dtype == CXL_DTYPE_F32) CXL_L2F(float, float);
   else if (x_dtype == CXL_DTYPE_BF16 && y_dtype == CXL_DTYPE_BF16) CXL_L2F(bf, bf);
   else if (x_dtype == CXL_DTYPE_BF16 && y_dtype == CXL_DTYPE_F32) CXL_L2F(bf, float);
+  else if (x_dtype == CXL_DTYPE_F32 && y_dtype == CXL_DTYPE_F16) CXL_L2F(float, __half);      // fp16 autocast (--precision amp)
+  else if (x_dtype == CXL_DTYPE_F16 && y_dtype == CXL_DTYPE_F16) CXL_L2F(__half, __half);
+  else if (x_dtype == CXL_DTYPE_F16 && y_dtype == CXL_DTYPE_F32) CXL_L2F(__half, float);
   else return CXL_ERR_INVALID_ARG;
 #undef CXL_L2F
   CXL_CUDA_CHECK(cudaGetLastError());
@@ -149,6 +174,9 @@ static int l2norm_bwd_out(const void* y, const void* g, const float* inv_norm, l
   else if (dx_dtype == CXL_DTYPE_BF16)
     l2norm_bwd_kernel<TY, TG, __nv_bfloat16><<<grid, 256, 0, CXL_COUNTED(stream)>>>(
         static_cast<const TY*>(y), static_cast<const TG*>(g), inv_norm, rows, D, static_cast<__nv_bfloat16*>(dx));
+  else if (dx_dtype == CXL_DTYPE_F16)
+    l2norm_bwd_kernel<TY, TG, __half><<<grid, 256, 0, CXL_COUNTED(stream)>>>(
+        static_cast<const TY*>(y), static_cast<const TG*>(g), inv_norm, rows, D, static_cast<__half*>(dx));
   else
     return CXL_ERR_INVALID_ARG;
   CXL_CUDA_CHECK(cudaGetLastError());
@@ -170,6 +198,10 @@ int l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const flo
     return l2norm_bwd_out<float, float>(y, g, inv_norm, rows, D, dx, dx_dtype, grid, stream);
   if (y_dtype == CXL_DTYPE_F32 && g_dtype == CXL_DTYPE_BF16)
     return l2norm_bwd_out<float, bf>(y, g, inv_norm, rows, D, dx, dx_dtype, grid, stream);
+  if (y_dtype == CXL_DTYPE_F16 && g_dtype == CXL_DTYPE_F16)
+    return l2norm_bwd_out<__half, __half>(y, g, inv_norm, rows, D, dx, dx_dtype, grid, stream);
+  if (y_dtype == CXL_DTYPE_F16 && g_dtype == CXL_DTYPE_F32)
+    return l2norm_bwd_out<__half, float>(y, g, inv_norm, rows, D, dx, dx_dtype, grid, stream);
   return CXL_ERR_INVALID_ARG;
 }
 

@@ -29,6 +29,20 @@ template <> struct Vec<__nv_bfloat16> {
     }
   }
 };
+template <> struct Vec<__half> {
+  static constexpr int N = 8;
+  __device__ static void load(const __half* p, float (&o)[8]) {
+    const uint4 v = __ldg(reinterpret_cast<const uint4*>(p));
+    const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const float2 f = __half22float2(*reinterpret_cast<const __half2*>(&w[i]));
+      o[2 * i] = f.x;
+      o[2 * i + 1] = f.y;
+    }
+  }
+};
+__device__ __forceinline__ float to_f32(__half x) { return __half2float(x); }
 __device__ __forceinline__ float to_f32(float x) { return x; }
 __device__ __forceinline__ float to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
 
@@ -156,24 +170,27 @@ __global__ void __launch_bounds__(128) maxsim_bwd_dimg_kernel(const BwdParams p,
 int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                       const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
                       float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes,
-                      cudaStream_t stream);
+                      int f16, const float* w_scale, cudaStream_t stream);
 
 // arg_row_off != 0: txt / w / dtxt point at a slice of Bt texts whose first flat text-token row is `arg_row_off`
 // inside the forward's argmax rows (pitch ld_arg); only dTxt can be computed from a row slice.
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
                float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, int force_generic, void* ws,
-               size_t ws_bytes, cudaStream_t stream) {
+               size_t ws_bytes, const float* w_scale, cudaStream_t stream) {
   if (ld_pairs < Bi + k_off || k_off < 0) return CXL_ERR_INVALID_ARG;
   if (arg_row_off < 0 || ld_arg < arg_row_off + static_cast<long long>(Bt) * T) return CXL_ERR_INVALID_ARG;
   if (arg_row_off != 0 && dimg != nullptr) return CXL_ERR_INVALID_ARG;
-  if (dtype == CXL_DTYPE_BF16 && !force_generic) {
+  const bool half16 = dtype == CXL_DTYPE_BF16 || dtype == CXL_DTYPE_F16;
+  if (half16 && !force_generic) {
     // fast path: TMA-staged streaming kernels; shapes it does not cover fall through to the generic kernels
     const int rc = maxsim_bwd_stream(txt, img, argmax, ld_arg, arg_row_off, w, Bt, Bi, T, P, D, p_stride, ld_pairs,
-                                     k_off, dtxt, accumulate_txt, dimg, accumulate_img, ws, ws_bytes, stream);
+                                     k_off, dtxt, accumulate_txt, dimg, accumulate_img, ws, ws_bytes,
+                                     dtype == CXL_DTYPE_F16, w_scale, stream);
     if (rc != CXL_ERR_UNSUPPORTED) return rc;
   }
-  const int V = dtype == CXL_DTYPE_BF16 ? 8 : 4;
+  // (the generic kernels multiply with the fp32 pair weight: w_scale does not apply)
+  const int V = half16 ? 8 : 4;
   if (D % V != 0) return CXL_ERR_UNSUPPORTED;
   BwdParams p;
   p.txt = txt; p.img = img; p.ld_arg = ld_arg; p.w = w;
@@ -187,6 +204,7 @@ int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long l
     const long long rows = static_cast<long long>(Bt) * T;
     dim3 grid(static_cast<unsigned>((rows + 7) / 8), (D + 32 * V - 1) / (32 * V));
     if (dtype == CXL_DTYPE_BF16) maxsim_bwd_dtxt_kernel<__nv_bfloat16><<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
+    else if (dtype == CXL_DTYPE_F16) maxsim_bwd_dtxt_kernel<__half><<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
     else maxsim_bwd_dtxt_kernel<float><<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
     CXL_CUDA_CHECK(cudaGetLastError());
   }
@@ -197,7 +215,11 @@ int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long l
     const size_t smem = static_cast<size_t>(P) * DS * 4;
     if (smem > 220 * 1024) return CXL_ERR_UNSUPPORTED;
     dim3 grid(Bi, (D + DS - 1) / DS);
-    if (dtype == CXL_DTYPE_BF16) {
+    if (dtype == CXL_DTYPE_F16) {
+      CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_bwd_dimg_kernel<__half>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          static_cast<int>(smem)));
+      maxsim_bwd_dimg_kernel<__half><<<grid, DS, smem, CXL_COUNTED(stream)>>>(p, DS);
+    } else if (dtype == CXL_DTYPE_BF16) {
       CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_bwd_dimg_kernel<__nv_bfloat16>,
                                           cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem)));
       maxsim_bwd_dimg_kernel<__nv_bfloat16><<<grid, DS, smem, CXL_COUNTED(stream)>>>(p, DS);

@@ -38,6 +38,8 @@ struct Dimg4StepsParams {
   uint16_t* blk_units;     // [n_img][walks] bytes / 16 of each block that are in use (0: empty walk)
   int cap_words;           // table words that fit the pre-pass's shared-memory staging (larger tables go straight to global)
   int per_warp_words;
+  int f16;                 // 16-bit pair weights are fp16 (fp16 operands) instead of bf16
+  const float* w_scale;    // device [s, 1/s] or null
 };
 
 // Step table of one (image, walk):
@@ -93,9 +95,10 @@ __global__ void __launch_bounds__(128) dimg4_steps_kernel(const Dimg4StepsParams
     const int rem0 = r_lo - m_lo * p.T;
     const int ntext = (rem0 + nrows - 1) / p.T + 1;
     const float* wcol = p.w + static_cast<size_t>(m_lo) * p.ld_pairs + kcol;
+    const float w_s = p.w_scale != nullptr ? __ldg(p.w_scale) : 1.f;
     if (ntext <= rows_max) {                                 // always, unless T == 1 and the walk starts mid-text
       for (int i = lane; i < ntext; i += 32)
-        srow[i] = __bfloat16_as_ushort(__float2bfloat16_rn(__ldg(wcol + static_cast<size_t>(i) * p.ld_pairs)));
+        srow[i] = static_cast<uint16_t>(cvt_w16(__ldg(wcol + static_cast<size_t>(i) * p.ld_pairs) * w_s, p.f16));
       __syncwarp();
       const float invT = 1.0f / static_cast<float>(p.T);
       for (int r = lane; r < nrows; r += 32) {
@@ -105,7 +108,7 @@ __global__ void __launch_bounds__(128) dimg4_steps_kernel(const Dimg4StepsParams
       }
     } else {
       for (int r = lane; r < nrows; r += 32)
-        wrow[r] = __bfloat16_as_ushort(__float2bfloat16_rn(__ldg(wcol + static_cast<size_t>((rem0 + r) / p.T) * p.ld_pairs)));
+        wrow[r] = static_cast<uint16_t>(cvt_w16(__ldg(wcol + static_cast<size_t>((rem0 + r) / p.T) * p.ld_pairs) * w_s, p.f16));
     }
   }
   __syncwarp();
@@ -200,6 +203,7 @@ struct Dimg4Params {
   int P, D;
   float* dimg;
   int accumulate_img;
+  const float* w_scale;
 };
 
 struct __align__(8) Dimg4Barriers {
@@ -227,21 +231,25 @@ __device__ __forceinline__ void row_load(uint4& v, uint32_t ring_lane, uint32_t 
   }
 }
 // fhfma8_lo as a volatile asm: keeps both row loads of a pair ahead of the first FMA group
+#define CXL_FHFMA8_V(TY)                                                                                               \
+  asm volatile("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"                                           \
+      "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"   \
+      "mov.b32 {wl, wh}, %12;\n\t"                                                                                   \
+      "fma.rn.f32." TY " %0, x0, wl, %0;\n\t fma.rn.f32." TY " %1, x1, wl, %1;\n\t"                                  \
+      "fma.rn.f32." TY " %2, x2, wl, %2;\n\t fma.rn.f32." TY " %3, x3, wl, %3;\n\t"                                  \
+      "fma.rn.f32." TY " %4, x4, wl, %4;\n\t fma.rn.f32." TY " %5, x5, wl, %5;\n\t"                                  \
+      "fma.rn.f32." TY " %6, x6, wl, %6;\n\t fma.rn.f32." TY " %7, x7, wl, %7;\n\t}"                                 \
+      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])               \
+      : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e))
+template <bool F16>
 __device__ __forceinline__ void fhfma8_lo_v(float (&a)[8], const uint4& v, uint32_t e) {
-  asm volatile("{\n\t.reg .b16 x0, x1, x2, x3, x4, x5, x6, x7, wl, wh;\n\t"
-      "mov.b32 {x0, x1}, %8;\n\t mov.b32 {x2, x3}, %9;\n\t mov.b32 {x4, x5}, %10;\n\t mov.b32 {x6, x7}, %11;\n\t"
-      "mov.b32 {wl, wh}, %12;\n\t"
-      "fma.rn.f32.bf16 %0, x0, wl, %0;\n\t fma.rn.f32.bf16 %1, x1, wl, %1;\n\t"
-      "fma.rn.f32.bf16 %2, x2, wl, %2;\n\t fma.rn.f32.bf16 %3, x3, wl, %3;\n\t"
-      "fma.rn.f32.bf16 %4, x4, wl, %4;\n\t fma.rn.f32.bf16 %5, x5, wl, %5;\n\t"
-      "fma.rn.f32.bf16 %6, x6, wl, %6;\n\t fma.rn.f32.bf16 %7, x7, wl, %7;\n\t}"
-      : "+f"(a[0]), "+f"(a[1]), "+f"(a[2]), "+f"(a[3]), "+f"(a[4]), "+f"(a[5]), "+f"(a[6]), "+f"(a[7])
-      : "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w), "r"(e));
+  if (F16) CXL_FHFMA8_V("f16");
+  else CXL_FHFMA8_V("bf16");
 }
 
 // Warps [0, NW): consumers (quarter warp o = 4 warp + lane / 8 owns patches [o NPO, o NPO + NPO) of the CTA's NIMG
 // images); warp NW issues the loads.  PF: the row reads of pair i+1 are issued before the FMAs of pair i.
-template <int NW, int NPO, int NIMG, bool PRED, bool PF>
+template <int NW, int NPO, int NIMG, bool PRED, bool PF, bool F16>
 __global__ void __launch_bounds__((NW + 1) * 32, 1)
 dimg4_gather_kernel(const __grid_constant__ CUtensorMap tmTxt, const Dimg4Params p) {
   constexpr int DS = 64;
@@ -364,15 +372,15 @@ dimg4_gather_kernel(const __grid_constant__ CUtensorMap tmTxt, const Dimg4Params
                 uint4 na, nb;
                 row_load<false>(na, ring_lane, nxt.x);
                 row_load<false>(nb, ring_lane, nxt.y);
-                fhfma8_lo_v(acc[c][j], va, cur.x);
-                fhfma8_lo_v(acc[c][j], vb, cur.y);
+                fhfma8_lo_v<F16>(acc[c][j], va, cur.x);
+                fhfma8_lo_v<F16>(acc[c][j], vb, cur.y);
                 va = na;
                 vb = nb;
               } else {
                 row_load<PRED>(va, ring_lane, cur.x);
                 row_load<PRED>(vb, ring_lane, cur.y);
-                fhfma8_lo_v(acc[c][j], va, cur.x);
-                fhfma8_lo_v(acc[c][j], vb, cur.y);
+                fhfma8_lo_v<F16>(acc[c][j], va, cur.x);
+                fhfma8_lo_v<F16>(acc[c][j], vb, cur.y);
               }
               cur = nxt;
             }
@@ -399,8 +407,9 @@ dimg4_gather_kernel(const __grid_constant__ CUtensorMap tmTxt, const Dimg4Params
         const int q = owner * NPO + j;
         if (q < p.P) {
           float* o = p.dimg + (static_cast<size_t>(p.chunk_k0 + kl) * p.P + q) * p.D + d0 + (lane & 7) * 8;
-          float4 lo = make_float4(acc[i][j][0], acc[i][j][1], acc[i][j][2], acc[i][j][3]);
-          float4 hi = make_float4(acc[i][j][4], acc[i][j][5], acc[i][j][6], acc[i][j][7]);
+          const float w_inv = p.w_scale != nullptr ? __ldg(p.w_scale + 1) : 1.f;
+          float4 lo = make_float4(acc[i][j][0] * w_inv, acc[i][j][1] * w_inv, acc[i][j][2] * w_inv, acc[i][j][3] * w_inv);
+          float4 hi = make_float4(acc[i][j][4] * w_inv, acc[i][j][5] * w_inv, acc[i][j][6] * w_inv, acc[i][j][7] * w_inv);
           if (p.accumulate_img) {
             const float4 a = *reinterpret_cast<const float4*>(o);
             const float4 b = *reinterpret_cast<const float4*>(o + 4);
@@ -471,36 +480,41 @@ long long dimg4_bytes_per_image(const Dimg4Geom& g) {
   return static_cast<long long>(g.walks) * (g.blk_stride + 2);
 }
 
-template <int NW, int NPO, int NIMG>
-static int launch_gather4(const CUtensorMap& tm, const Dimg4Params& gp, dim3 grid, int smem_bytes, bool pred,
-                          cudaStream_t stream) {
-  if (pred) {
-    auto kern = dimg4_gather_kernel<NW, NPO, NIMG, true, false>;
-    CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, (NW + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, gp);
-  } else {
-    auto kern = dimg4_gather_kernel<NW, NPO, NIMG, false, false>;
-    CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    kern<<<grid, (NW + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, gp);
-  }
+template <int NW, int NPO, int NIMG, bool PRED, bool F16>
+static int launch_gather4_k(const CUtensorMap& tm, const Dimg4Params& gp, dim3 grid, int smem_bytes, cudaStream_t stream) {
+  auto kern = dimg4_gather_kernel<NW, NPO, NIMG, PRED, false, F16>;
+  CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  kern<<<grid, (NW + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, gp);
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
+}
+// fp16 operands are built for the default variants only (the CXL_DIMG_CFG experiments are bf16)
+template <int NW, int NPO, int NIMG, bool WITH_F16>
+static int launch_gather4(const CUtensorMap& tm, const Dimg4Params& gp, dim3 grid, int smem_bytes, bool pred, int f16,
+                          cudaStream_t stream) {
+  if (f16) {
+    if (!WITH_F16) return CXL_ERR_UNSUPPORTED;
+    return launch_gather4_k<NW, NPO, NIMG, false, WITH_F16>(tm, gp, grid, smem_bytes, stream);
+  }
+  if (pred) return launch_gather4_k<NW, NPO, NIMG, true, false>(tm, gp, grid, smem_bytes, stream);
+  return launch_gather4_k<NW, NPO, NIMG, false, false>(tm, gp, grid, smem_bytes, stream);
 }
 
 // dImg of images [k_off, k_off + Bi) in chunks of `cap` images (scratch = cap * dimg4_bytes_per_image)
 int launch_dimg_v4(const void* txt, const void* argmax, long long ld_arg, const float* w, int Bt, int Bi, int T, int P,
                    int D, int ld_pairs, int k_off, float* dimg, int accumulate_img, const Dimg4Geom& g, void* scratch,
-                   long long cap, int max_smem, cudaStream_t stream) {
+                   long long cap, int max_smem, int f16, const float* w_scale, cudaStream_t stream) {
   const int rows = Bt * T;
   const bool u16 = P > 256;
   CUtensorMap tm;
-  int rc = make_tmap_plain(&tm, txt, rows, D, 64, g.box_rows);
+  int rc = make_tmap_plain(&tm, txt, rows, D, 64, g.box_rows, f16);
   if (rc != CXL_OK) return rc;
 
   Dimg4StepsParams sp;
   memset(&sp, 0, sizeof(sp));
   sp.argmax = argmax; sp.ld_arg = ld_arg; sp.w = w; sp.ld_pairs = ld_pairs;
   sp.T = T; sp.P = P; sp.rows = rows; sp.g = g;
+  sp.f16 = f16 ? 1 : 0; sp.w_scale = w_scale;
   const long long units_bytes = (cap * g.walks * 2 + 255) / 256 * 256;
   sp.blk_units = static_cast<uint16_t*>(scratch);
   sp.blocks = static_cast<uint8_t*>(scratch) + units_bytes;
@@ -515,7 +529,7 @@ int launch_dimg_v4(const void* txt, const void* argmax, long long ld_arg, const 
   Dimg4Params gp;
   memset(&gp, 0, sizeof(gp));
   gp.blocks = sp.blocks; gp.blk_units = sp.blk_units; gp.g = g;
-  gp.P = P; gp.D = D; gp.dimg = dimg; gp.accumulate_img = accumulate_img;
+  gp.P = P; gp.D = D; gp.dimg = dimg; gp.accumulate_img = accumulate_img; gp.w_scale = w_scale;
   const int smem_bytes = kGatherSlack + g.ring * g.sub_bytes + g.nbuf * g.blk_stride;
   if (smem_bytes > max_smem) return CXL_ERR_UNSUPPORTED;
   const bool pred = env_int("CXL_DIMG_PRED", 0) != 0;
@@ -537,13 +551,13 @@ int launch_dimg_v4(const void* txt, const void* argmax, long long ld_arg, const 
     gp.chunk_k0 = k0;
     gp.chunk_n = n;
     dim3 grid(D / 64, (n + g.nimg - 1) / g.nimg);
-    if (g.nw == 17 && g.nimg == 3) rc = launch_gather4<17, 3, 3>(tm, gp, grid, smem_bytes, pred, stream);
-    else if (g.nw == 17) rc = launch_gather4<17, 3, 2>(tm, gp, grid, smem_bytes, pred, stream);
-    else if (g.nw == 25) rc = launch_gather4<25, 2, 2>(tm, gp, grid, smem_bytes, pred, stream);
-    else if (g.nw == 13 && g.nimg == 3) rc = launch_gather4<13, 4, 3>(tm, gp, grid, smem_bytes, pred, stream);
-    else if (g.nw == 13) rc = launch_gather4<13, 4, 2>(tm, gp, grid, smem_bytes, pred, stream);
-    else if (g.npo == 4) rc = launch_gather4<19, 4, 2>(tm, gp, grid, smem_bytes, pred, stream);
-    else rc = launch_gather4<19, 8, 1>(tm, gp, grid, smem_bytes, pred, stream);
+    if (g.nw == 17 && g.nimg == 3) rc = launch_gather4<17, 3, 3, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else if (g.nw == 17) rc = launch_gather4<17, 3, 2, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else if (g.nw == 25) rc = launch_gather4<25, 2, 2, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else if (g.nw == 13 && g.nimg == 3) rc = launch_gather4<13, 4, 3, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else if (g.nw == 13) rc = launch_gather4<13, 4, 2, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else if (g.npo == 4) rc = launch_gather4<19, 4, 2, false>(tm, gp, grid, smem_bytes, pred, f16, stream);
+    else rc = launch_gather4<19, 8, 1, true>(tm, gp, grid, smem_bytes, pred, f16, stream);
     if (rc != CXL_OK) return rc;
   }
   return CXL_OK;

@@ -43,6 +43,9 @@ struct BwdV2Params {
   int hdr_words, block_bytes;
   int chunk_k0;         // first image of the chunk (index into dimg)
   int chunk_n;          // images in the chunk
+  int f16;              // operands (and the 16-bit pair weights) are fp16 instead of bf16
+  const float* w_scale; // device [s, 1/s] or null: power of two applied to the pair weights before the 16-bit rounding
+                        // (keeps fp16 weights in range whatever the loss scale), undone exactly when results are stored
 };
 
 struct __align__(8) V2Barriers {
@@ -58,7 +61,7 @@ struct __align__(8) V2Barriers {
 // image AND the CTA's slice of that image's argmax row (ROWS contiguous elements, one bulk copy), so no
 // consumer ever waits on a global load for its indices.  Lane = 8*qw + l8: quarter qw handles rows 4*jj + qw
 // (jj = 0..7) of its warp, l8 selects the 8-channel chunk of the 64-wide slice.
-template <int NWC, bool U16>
+template <int NWC, bool U16, bool F16>
 __global__ void __launch_bounds__((NWC + 1) * 32, 1)
 maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2Params p) {
   constexpr int DS = 64;
@@ -117,6 +120,8 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
 
   // image blocks after the first continue from the partial sums in dTxt, so the additions happen in the same
   // order whatever the block size
+  const float w_s = p.w_scale != nullptr ? __ldg(p.w_scale) : 1.f;       // powers of two: scaling is exact
+  const float w_inv = p.w_scale != nullptr ? __ldg(p.w_scale + 1) : 1.f;
   float acc[8][8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
@@ -125,8 +130,8 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
       const float* o = p.dtxt + static_cast<size_t>(r) * p.D + d0 + (lane & 7) * 8;
       const float4 a = *reinterpret_cast<const float4*>(o);
       const float4 b = *reinterpret_cast<const float4*>(o + 4);
-      acc[j][0] = a.x; acc[j][1] = a.y; acc[j][2] = a.z; acc[j][3] = a.w;
-      acc[j][4] = b.x; acc[j][5] = b.y; acc[j][6] = b.z; acc[j][7] = b.w;
+      acc[j][0] = a.x * w_s; acc[j][1] = a.y * w_s; acc[j][2] = a.z * w_s; acc[j][3] = a.w * w_s;
+      acc[j][4] = b.x * w_s; acc[j][5] = b.y * w_s; acc[j][6] = b.z * w_s; acc[j][7] = b.w * w_s;
     } else {
 #pragma unroll
       for (int i = 0; i < 8; ++i) acc[j][i] = 0.f;
@@ -160,7 +165,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
   // entries of image 0
   mbar_wait(full0, 0);
   // entry = slab row offset << 16 | bf16(w): bytes (q*128) when P <= 256, 16-byte units (q*8) otherwise
-  sts32(ent_st, pack_entry_lo(wr[0], ldq_smem(smem0 + q_off) * (U16 ? 8u : 128u)));
+  sts32(ent_st, pack_entry_lo(wr[0] * w_s, ldq_smem(smem0 + q_off) * (U16 ? 8u : 128u), F16));
   __syncwarp();
 
   int stage = 0;                 // stage of image k
@@ -180,7 +185,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
         if (k + 1 < Bi) {
           mbar_wait(full0 + 8 * nstage, nphase);
           sts32(ent_st + ((b & 1) ^ 1) * 128,
-                pack_entry_lo(wr[(b + 1) & 3], ldq_smem(smem0 + nstage * stage_bytes + q_off) * (U16 ? 8u : 128u)));
+                pack_entry_lo(wr[(b + 1) & 3] * w_s, ldq_smem(smem0 + nstage * stage_bytes + q_off) * (U16 ? 8u : 128u), F16));
         }
         wr[b] = __ldg(wptr + min(k + 4, Bi - 1));
         const uint32_t stl = stl0 + stage * stage_bytes;
@@ -188,7 +193,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
 #pragma unroll
         for (int jj = 0; jj < 8; ++jj) {
           const uint4 v = lds128(stl + (U16 ? ((e[jj] >> 16) << 4) : (e[jj] >> 16)));   // u8: one LEA.HI
-          fhfma8_lo(acc[jj], v, e[jj]);
+          fhfma8_lo<F16>(acc[jj], v, e[jj]);
         }
         __syncwarp();
         if (lane == 0) mbar_arrive(empty0 + 8 * stage);
@@ -202,8 +207,8 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
     const int r = r0 + warp * 32 + 4 * jj + qw;
     if (r < p.rows) {
       float* o = p.dtxt + static_cast<size_t>(r) * p.D + d0 + (lane & 7) * 8;
-      *reinterpret_cast<float4*>(o) = make_float4(acc[jj][0], acc[jj][1], acc[jj][2], acc[jj][3]);
-      *reinterpret_cast<float4*>(o + 4) = make_float4(acc[jj][4], acc[jj][5], acc[jj][6], acc[jj][7]);
+      *reinterpret_cast<float4*>(o) = make_float4(acc[jj][0] * w_inv, acc[jj][1] * w_inv, acc[jj][2] * w_inv, acc[jj][3] * w_inv);
+      *reinterpret_cast<float4*>(o + 4) = make_float4(acc[jj][4] * w_inv, acc[jj][5] * w_inv, acc[jj][6] * w_inv, acc[jj][7] * w_inv);
     }
   }
 }
@@ -233,6 +238,8 @@ struct DimgListParams {
   int Bt, T, P, rows, n_st;
   int hdr_words, block_bytes;
   uint8_t* lists;       // [n_img][n_st][block_bytes]
+  int f16;
+  const float* w_scale;
 };
 
 template <bool U16>
@@ -255,6 +262,7 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgLi
   const int rows0 = s * kStRows;
   const int nrows = min(kStRows, p.rows - rows0);
   const uint32_t q_max = static_cast<uint32_t>(p.P - 1);
+  const float w_s = p.w_scale != nullptr ? __ldg(p.w_scale) : 1.f;
 
   for (int i = lane; i < p.hdr_words; i += 32) cur[i] = 0u;
   __syncwarp();
@@ -287,8 +295,8 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgLi
       const int nb = p.T - rem;                            // rows of this lane that still belong to text m
       const float w0 = __ldg(p.w + static_cast<size_t>(m) * p.ld_pairs + kcol);
       const float w1 = (nb < 16) ? __ldg(p.w + static_cast<size_t>(m + 1) * p.ld_pairs + kcol) : 0.f;
-      const uint32_t b0 = __bfloat16_as_ushort(__float2bfloat16_rn(w0));
-      const uint32_t b1 = __bfloat16_as_ushort(__float2bfloat16_rn(w1));
+      const uint32_t b0 = cvt_w16(w0 * w_s, p.f16);
+      const uint32_t b1 = cvt_w16(w1 * w_s, p.f16);
 #pragma unroll
       for (int i = 0; i < 16; i += 2) wpk[i >> 1] = (i < nb ? b0 : b1) | ((i + 1 < nb ? b0 : b1) << 16);
 #pragma unroll
@@ -310,7 +318,7 @@ __global__ void __launch_bounds__(256) maxsim_bwd_dimg_lists_kernel(const DimgLi
           ++rem;
           const uint32_t q = U16 ? ((a[i >> 1] >> (16 * (i & 1))) & 0xFFFFu) : ((a[i >> 2] >> (8 * (i & 3))) & 0xFFu);
           atomicAdd(&cur[min(q, q_max)], 1u);
-          wb = __bfloat16_as_ushort(__float2bfloat16_rn(wv));
+          wb = cvt_w16(wv * w_s, p.f16);
         }
         if (i & 1) wpk[i >> 1] |= wb << 16;
         else wpk[i >> 1] = wb;
@@ -373,7 +381,7 @@ struct __align__(8) DimgBarriers {
 
 // Warps [0, NW): consumers (quarter warp o = 4 warp + lane / 8 owns patches [o NPO, o NPO + NPO) of the CTA's NIMG
 // images); warp NW issues the loads.  Stage = [512 x 64 bf16 super-tile of text rows | NIMG list blocks].
-template <int NW, int NPO, int NIMG>
+template <int NW, int NPO, int NIMG, bool F16>
 __global__ void __launch_bounds__((NW + 1) * 32, 1)
 maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2Params p) {
   constexpr int DS = 64;
@@ -472,8 +480,8 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
                        : "=&r"(ea), "=&r"(eb) : "r"(ep), "r"(it), "r"(len), "r"(it + 1));
           const uint4 va = lds128(row_base + (ea >> 16));
           const uint4 vb = lds128(row_base + (eb >> 16));
-          fhfma8_lo(acc[i][j], va, ea);
-          fhfma8_lo(acc[i][j], vb, eb);
+          fhfma8_lo<F16>(acc[i][j], va, ea);
+          fhfma8_lo<F16>(acc[i][j], vb, eb);
         }
         if (it < maxlen) {
           uint32_t ea;
@@ -481,7 +489,7 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
                        "setp.lt.s32 pa, %2, %3;\n\t mov.b32 %0, 0;\n\t @pa ld.shared.b32 %0, [%1];\n\t}"
                        : "=&r"(ea) : "r"(ep), "r"(it), "r"(len));
           const uint4 va = lds128(row_base + (ea >> 16));
-          fhfma8_lo(acc[i][j], va, ea);
+          fhfma8_lo<F16>(acc[i][j], va, ea);
         }
       }
     }
@@ -498,8 +506,9 @@ maxsim_bwd_dimg_v3_kernel(const __grid_constant__ CUtensorMap tmTxt, const BwdV2
         const int q = owner * NPO + j;
         if (q < p.P) {
           float* o = p.dimg + (static_cast<size_t>(p.chunk_k0 + kl) * p.P + q) * p.D + d0 + (lane & 7) * 8;
-          float4 lo = make_float4(acc[i][j][0], acc[i][j][1], acc[i][j][2], acc[i][j][3]);
-          float4 hi = make_float4(acc[i][j][4], acc[i][j][5], acc[i][j][6], acc[i][j][7]);
+          const float w_inv = p.w_scale != nullptr ? __ldg(p.w_scale + 1) : 1.f;
+          float4 lo = make_float4(acc[i][j][0] * w_inv, acc[i][j][1] * w_inv, acc[i][j][2] * w_inv, acc[i][j][3] * w_inv);
+          float4 hi = make_float4(acc[i][j][4] * w_inv, acc[i][j][5] * w_inv, acc[i][j][6] * w_inv, acc[i][j][7] * w_inv);
           if (p.accumulate_img) {
             const float4 a = *reinterpret_cast<const float4*>(o);
             const float4 b = *reinterpret_cast<const float4*>(o + 4);
@@ -533,15 +542,15 @@ static EncodeTiledFnV2 encode_fn_v2() {
 }
 
 // [rows, D] bf16 row-major, box = box_cols x box_rows, no swizzle (rows land densely, box_cols*2 bytes apart)
-int make_tmap_plain(CUtensorMap* out, const void* base, long long rows, int D, int box_cols, int box_rows) {
+int make_tmap_plain(CUtensorMap* out, const void* base, long long rows, int D, int box_cols, int box_rows, int f16) {
   EncodeTiledFnV2 fn = encode_fn_v2();
   if (fn == nullptr) return CXL_ERR_CUDA;
   cuuint64_t gdim[2] = {static_cast<cuuint64_t>(D), static_cast<cuuint64_t>(rows)};
   cuuint64_t gstride[1] = {static_cast<cuuint64_t>(D) * 2};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(box_cols), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = fn(out, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled (bwd)");
@@ -557,7 +566,7 @@ int env_int(const char* name, int dflt) {
   return (s != nullptr && *s != 0) ? atoi(s) : dflt;
 }
 
-template <int NWC, bool U16>
+template <int NWC, bool U16, bool F16>
 static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStream_t stream) {
   constexpr int DS = 64;
   constexpr int ROWS = NWC * 32;
@@ -573,9 +582,9 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
   p.stages = stages > 6 ? 6 : stages;
   const int smem_bytes = overhead + p.stages * p.stage_bytes;
   CUtensorMap tm;
-  int rc = make_tmap_plain(&tm, img, static_cast<long long>(p.Bi) * p.p_stride, p.D, DS, box_rows);
+  int rc = make_tmap_plain(&tm, img, static_cast<long long>(p.Bi) * p.p_stride, p.D, DS, box_rows, F16);
   if (rc != CXL_OK) return rc;
-  auto kern = maxsim_bwd_dtxt_v2_kernel<NWC, U16>;
+  auto kern = maxsim_bwd_dtxt_v2_kernel<NWC, U16, F16>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
   dim3 grid((p.rows + ROWS - 1) / ROWS, p.D / DS);
   // Image blocks: every CTA of a D slice streams the same [P,64] slabs, but the CTAs of later waves start
@@ -600,7 +609,7 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
 }
 
 // One chunk of images: lists pre-pass, then the gather kernel.  `p.lists` is scratch for chunk_cap images.
-template <int NW, int NPO, int NIMG>
+template <int NW, int NPO, int NIMG, bool F16>
 static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chunk_cap, cudaStream_t stream) {
   constexpr int DS = 64;
   p.stage_bytes = kStRows * DS * 2 + NIMG * p.block_bytes;           // tile | list blocks
@@ -610,9 +619,9 @@ static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chun
   p.stages = stages > 4 ? 4 : stages;
   const int smem_bytes = overhead + p.stages * p.stage_bytes;
   CUtensorMap tm;
-  int rc = make_tmap_plain(&tm, txt, p.rows, p.D, DS, kStRows / 2);
+  int rc = make_tmap_plain(&tm, txt, p.rows, p.D, DS, kStRows / 2, F16);
   if (rc != CXL_OK) return rc;
-  auto kern = maxsim_bwd_dimg_v3_kernel<NW, NPO, NIMG>;
+  auto kern = maxsim_bwd_dimg_v3_kernel<NW, NPO, NIMG, F16>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
 
   DimgListParams lp;
@@ -620,6 +629,7 @@ static int launch_dimg_v3(const void* txt, BwdV2Params p, int max_smem, int chun
   lp.Bt = p.Bt; lp.T = p.T; lp.P = p.P; lp.rows = p.rows; lp.n_st = p.n_st;
   lp.hdr_words = p.hdr_words; lp.block_bytes = p.block_bytes;
   lp.lists = const_cast<uint8_t*>(p.lists);
+  lp.f16 = p.f16; lp.w_scale = p.w_scale;
   const int lists_smem = 8 * (2 * lp.hdr_words + kStRows + (p.argmax_u16 ? 256 : 128) + 256) * 4;
   auto lkern = p.argmax_u16 ? maxsim_bwd_dimg_lists_kernel<true> : maxsim_bwd_dimg_lists_kernel<false>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(lkern, cudaFuncAttributeMaxDynamicSharedMemorySize, lists_smem));
@@ -731,7 +741,7 @@ size_t maxsim_bwd_workspace_bytes(int Bt, int Bi, int T, int P, int D) {
 int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                       const float* w, int Bt, int Bi, int T, int P, int D, int p_stride, int ld_pairs, int k_off,
                       float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, void* ws, size_t ws_bytes,
-                      cudaStream_t stream) {
+                      int f16, const float* w_scale, cudaStream_t stream) {
   if (!stream_path_covers(txt, img, Bt, T, P, D)) return CXL_ERR_UNSUPPORTED;
   const int es = P > 256 ? 2 : 1;
   if ((arg_row_off * es) % 16 != 0) return CXL_ERR_UNSUPPORTED;     // bulk copies of argmax runs need 16 B alignment
@@ -744,13 +754,15 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
   p.rows = Bt * T;
   p.ld_pairs = ld_pairs; p.k_off = k_off; p.argmax_u16 = P > 256;
   p.dtxt = dtxt; p.dimg = dimg; p.accumulate_img = accumulate_img; p.accumulate_txt = accumulate_txt;
+  p.f16 = f16 ? 1 : 0; p.w_scale = w_scale;
   int dev = 0, max_smem = 0;
   CXL_CUDA_CHECK(cudaGetDevice(&dev));
   CXL_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
 
   int rc = CXL_OK;
   if (dtxt != nullptr) {
-    rc = P > 256 ? launch_dtxt_v2<15, true>(img, p, max_smem, stream) : launch_dtxt_v2<15, false>(img, p, max_smem, stream);
+    if (f16) rc = P > 256 ? launch_dtxt_v2<15, true, true>(img, p, max_smem, stream) : launch_dtxt_v2<15, false, true>(img, p, max_smem, stream);
+    else rc = P > 256 ? launch_dtxt_v2<15, true, false>(img, p, max_smem, stream) : launch_dtxt_v2<15, false, false>(img, p, max_smem, stream);
     if (rc != CXL_OK) return rc;
   }
   if (dimg != nullptr && use_dimg4(P)) {
@@ -775,7 +787,7 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
       }
     }
     rc = launch_dimg_v4(txt, argmax, ld_arg, w, Bt, Bi, T, P, D, ld_pairs, k_off, dimg, accumulate_img, g, scratch, cap,
-                        max_smem, stream);
+                        max_smem, f16, w_scale, stream);
     if (ws == nullptr) {
       const cudaError_t fe = cudaFreeAsync(scratch, stream);
       if (rc == CXL_OK && fe != cudaSuccess) {
@@ -816,9 +828,16 @@ int maxsim_bwd_stream(const void* txt, const void* img, const void* argmax, long
       }
     }
     p.lists = static_cast<const uint8_t*>(scratch);
-    if (d.npo == 2) rc = launch_dimg_v3<25, 2, 2>(txt, p, max_smem, static_cast<int>(cap), stream);
-    else if (d.npo == 3) rc = launch_dimg_v3<25, 3, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
-    else rc = launch_dimg_v3<19, 8, 1>(txt, p, max_smem, static_cast<int>(cap), stream);
+    const int cap_i = static_cast<int>(cap);
+    if (f16) {
+      if (d.npo == 2) rc = launch_dimg_v3<25, 2, 2, true>(txt, p, max_smem, cap_i, stream);
+      else if (d.npo == 3) rc = launch_dimg_v3<25, 3, 1, true>(txt, p, max_smem, cap_i, stream);
+      else rc = launch_dimg_v3<19, 8, 1, true>(txt, p, max_smem, cap_i, stream);
+    } else {
+      if (d.npo == 2) rc = launch_dimg_v3<25, 2, 2, false>(txt, p, max_smem, cap_i, stream);
+      else if (d.npo == 3) rc = launch_dimg_v3<25, 3, 1, false>(txt, p, max_smem, cap_i, stream);
+      else rc = launch_dimg_v3<19, 8, 1, false>(txt, p, max_smem, cap_i, stream);
+    }
     if (ws == nullptr) {
       const cudaError_t fe = cudaFreeAsync(scratch, stream);
       if (rc == CXL_OK && fe != cudaSuccess) {

@@ -43,6 +43,7 @@ struct FwdTcParams {
   int b_block_bytes;     // n_tile * 128
   int mean_mode;
   int argmax_u16;
+  int f16;               // operands are fp16 instead of bf16 (same tiles, same rate; instruction descriptor formats differ)
   float* S;              // [Bt,Bi] pre-zeroed accumulator of row maxima sums
   float* cnt;            // [Bt,Bi] pre-zeroed count of non-zero maxima (or null)
   void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
@@ -181,7 +182,7 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
   } else if (warp == 1) {
     // ===================== MMA issuer =====================
     // whole warp runs the warp-uniform control flow (descriptors stay in uniform registers); one elected lane issues
-    const uint32_t idesc = umma_idesc_bf16(kBlockM, p.n_tile);
+    const uint32_t idesc = umma_idesc_bf16(kBlockM, p.n_tile, p.f16);
     const uint64_t desc_a0 = umma_smem_desc_sw128(smem_u32(smem_a));
     const uint64_t desc_r0 = umma_smem_desc_sw128(smem_u32(smem_ring));
     const uint32_t a_step = kABlockBytes >> 4;            // descriptor address units are 16 bytes
@@ -415,7 +416,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     // ===================== MMA issuer (even CTA only) =====================
     // The whole warp runs the (warp-uniform) control flow so that addresses and descriptors stay in the uniform
     // datapath; one elected lane issues the tcgen05 instructions.
-    const uint32_t idesc = umma_idesc_bf16(2 * kBlockM, p.n_tile);
+    const uint32_t idesc = umma_idesc_bf16(2 * kBlockM, p.n_tile, p.f16);
     const uint64_t desc_a0 = umma_smem_desc_sw128(smem_u32(smem_a));
     const uint64_t desc_b0 = umma_smem_desc_sw128(smem_u32(smem_ring));
     const uint32_t a_step = kABlockBytes >> 4;            // descriptor address units are 16 bytes
@@ -437,7 +438,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // both CTAs' epilogues drained this buffer
         tc_fence_after();
         const uint32_t tmem_d = tmem_base + buf * 256;
-        const uint32_t idesc_j = p.pack_g ? umma_idesc_bf16(2 * kBlockM, p.pack_n[j % p.pack_g]) : idesc;
+        const uint32_t idesc_j = p.pack_g ? umma_idesc_bf16(2 * kBlockM, p.pack_n[j % p.pack_g], p.f16) : idesc;
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_full[stage]), phase);
           tc_fence_after();
@@ -636,15 +637,15 @@ static EncodeTiledFn get_encode_fn() {
 }
 
 // [rows, D] bf16 row-major matrix, box = 64 columns x box_rows rows, 128-byte swizzle
-static int make_tmap(CUtensorMap* out, const void* base, long long rows, int D, int box_rows) {
+static int make_tmap(CUtensorMap* out, const void* base, long long rows, int D, int box_rows, int f16) {
   EncodeTiledFn fn = get_encode_fn();
   if (fn == nullptr) return CXL_ERR_CUDA;
   cuuint64_t gdim[2] = {static_cast<cuuint64_t>(D), static_cast<cuuint64_t>(rows)};
   cuuint64_t gstride[1] = {static_cast<cuuint64_t>(D) * 2};
   cuuint32_t box[2] = {static_cast<cuuint32_t>(kBlockK), static_cast<cuuint32_t>(box_rows)};
   cuuint32_t estr[2] = {1, 1};
-  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), gdim, gstride, box, estr,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+  CUresult r = fn(out, f16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                  const_cast<void*>(base), gdim, gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     set_cuda_error(cudaErrorInvalidValue, "cuTensorMapEncodeTiled");
@@ -658,13 +659,15 @@ static int round_up(int x, int m) { return (x + m - 1) / m * m; }
 int img_row_stride(int P) { return P <= 128 ? round_up(P, 8) : P; }
 
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, cudaStream_t stream) {
+                  float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, int f16,
+                  cudaStream_t stream) {
   if (D % kBlockK != 0 || D < kBlockK) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
   if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
   FwdTcParams p;
   memset(&p, 0, sizeof(p));
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
+  p.f16 = f16 ? 1 : 0;
   p.rows_a = Bt * T;
   p.num_kb = D / kBlockK;
   p.p_stride = img_row_stride(P);
@@ -749,9 +752,9 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       q.exp_mode = getenv("CXL_K1_EXP") ? atoi(getenv("CXL_K1_EXP")) : 0;
 #endif
       CUtensorMap tmA2, tmB2;
-      int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM);
+      int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM, p.f16);
       if (rc2 != CXL_OK) return rc2;
-      rc2 = make_tmap(&tmB2, img, static_cast<long long>(Bi) * q.p_stride, D, q.n_tile / 2);
+      rc2 = make_tmap(&tmB2, img, static_cast<long long>(Bi) * q.p_stride, D, q.n_tile / 2, p.f16);
       if (rc2 != CXL_OK) return rc2;
       const size_t npairs2 = static_cast<size_t>(Bt) * Bi;
       CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
@@ -795,9 +798,9 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   p.S = S; p.cnt = cnt; p.argmax = argmax; p.ld_arg = ld_arg; p.dbg = dbg;
 
   CUtensorMap tmA, tmB;
-  int rc = make_tmap(&tmA, txt, p.rows_a, D, kBlockM);
+  int rc = make_tmap(&tmA, txt, p.rows_a, D, kBlockM, p.f16);
   if (rc != CXL_OK) return rc;
-  rc = make_tmap(&tmB, img, static_cast<long long>(Bi) * p.p_stride, D, p.n_tile);
+  rc = make_tmap(&tmB, img, static_cast<long long>(Bi) * p.p_stride, D, p.n_tile, p.f16);
   if (rc != CXL_OK) return rc;
 
   const size_t npairs = static_cast<size_t>(Bt) * Bi;

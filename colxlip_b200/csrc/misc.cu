@@ -3,11 +3,23 @@
 
 namespace cxl {
 
-// src [items, n, D] (f32 or bf16, arbitrary item/row strides, unit channel stride)
-//   -> dst bf16 [items, n_pad, D] contiguous; rows n..n_pad-1 are zero.
-template <typename T>
-__global__ void pack_bf16_kernel(const T* __restrict__ src, long long item_stride, long long row_stride, int items,
-                                 int n, int n_pad, int D, __nv_bfloat16* __restrict__ dst) {
+// src [items, n, D] (f32, bf16 or f16, arbitrary item/row strides, unit channel stride)
+//   -> dst bf16 or f16 [items, n_pad, D] contiguous; rows n..n_pad-1 are zero.
+__device__ __forceinline__ float pk_to_f32(float x) { return x; }
+__device__ __forceinline__ float pk_to_f32(__nv_bfloat16 x) { return __bfloat162float(x); }
+__device__ __forceinline__ float pk_to_f32(__half x) { return __half2float(x); }
+__device__ __forceinline__ uint32_t pk_pair(float a, float b, __nv_bfloat16*) {
+  __nv_bfloat162 v = __floats2bfloat162_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+__device__ __forceinline__ uint32_t pk_pair(float a, float b, __half*) {
+  __half2 v = __floats2half2_rn(a, b);
+  return *reinterpret_cast<uint32_t*>(&v);
+}
+
+template <typename T, typename O>
+__global__ void pack_operand_kernel(const T* __restrict__ src, long long item_stride, long long row_stride, int items,
+                                    int n, int n_pad, int D, O* __restrict__ dst) {
   const int dq = D >> 2;   // groups of 4 channels
   const size_t total = static_cast<size_t>(items) * n_pad * dq;
   for (size_t i = blockIdx.x * static_cast<size_t>(blockDim.x) + threadIdx.x; i < total;
@@ -20,37 +32,53 @@ __global__ void pack_bf16_kernel(const T* __restrict__ src, long long item_strid
     if (r < n) {
       const T* s = src + it * item_stride + static_cast<long long>(r) * row_stride + c4 * 4;
 #pragma unroll
-      for (int j = 0; j < 4; ++j) v[j] = static_cast<float>(s[j]);
+      for (int j = 0; j < 4; ++j) v[j] = pk_to_f32(s[j]);
     }
-    __nv_bfloat162 lo = __floats2bfloat162_rn(v[0], v[1]);
-    __nv_bfloat162 hi = __floats2bfloat162_rn(v[2], v[3]);
     uint2 o;
-    o.x = *reinterpret_cast<uint32_t*>(&lo);
-    o.y = *reinterpret_cast<uint32_t*>(&hi);
+    o.x = pk_pair(v[0], v[1], static_cast<O*>(nullptr));
+    o.y = pk_pair(v[2], v[3], static_cast<O*>(nullptr));
     *reinterpret_cast<uint2*>(dst + (rr * D + c4 * 4)) = o;
   }
 }
 
-int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
-              int D, void* dst, cudaStream_t stream) {
+template <typename O>
+static int pack_to(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n,
+                   int n_pad, int D, O* dst, unsigned blocks, cudaStream_t stream) {
+  if (src_dtype == CXL_DTYPE_F32)
+    pack_operand_kernel<float, O><<<blocks, 256, 0, CXL_COUNTED(stream)>>>(
+        reinterpret_cast<const float*>(src), item_stride, row_stride, items, n, n_pad, D, dst);
+  else if (src_dtype == CXL_DTYPE_BF16)
+    pack_operand_kernel<__nv_bfloat16, O><<<blocks, 256, 0, CXL_COUNTED(stream)>>>(
+        reinterpret_cast<const __nv_bfloat16*>(src), item_stride, row_stride, items, n, n_pad, D, dst);
+  else if (src_dtype == CXL_DTYPE_F16)
+    pack_operand_kernel<__half, O><<<blocks, 256, 0, CXL_COUNTED(stream)>>>(
+        reinterpret_cast<const __half*>(src), item_stride, row_stride, items, n, n_pad, D, dst);
+  else
+    return CXL_ERR_INVALID_ARG;
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+int pack_operand(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n,
+                 int n_pad, int D, void* dst, int dst_dtype, cudaStream_t stream) {
   if (D % 4 != 0 || n_pad < n || items < 0) return CXL_ERR_INVALID_ARG;
   const size_t total = static_cast<size_t>(items) * n_pad * (D >> 2);
   if (total == 0) return CXL_OK;
   size_t blocks = (total + 255) / 256;
   const size_t cap = static_cast<size_t>(num_sms()) * 32;
   if (blocks > cap) blocks = cap;
-  if (src_dtype == CXL_DTYPE_F32)
-    pack_bf16_kernel<float><<<static_cast<unsigned>(blocks), 256, 0, CXL_COUNTED(stream)>>>(
-        reinterpret_cast<const float*>(src), item_stride, row_stride, items, n, n_pad, D,
-        reinterpret_cast<__nv_bfloat16*>(dst));
-  else if (src_dtype == CXL_DTYPE_BF16)
-    pack_bf16_kernel<__nv_bfloat16><<<static_cast<unsigned>(blocks), 256, 0, CXL_COUNTED(stream)>>>(
-        reinterpret_cast<const __nv_bfloat16*>(src), item_stride, row_stride, items, n, n_pad, D,
-        reinterpret_cast<__nv_bfloat16*>(dst));
-  else
-    return CXL_ERR_INVALID_ARG;
-  CXL_CUDA_CHECK(cudaGetLastError());
-  return CXL_OK;
+  if (dst_dtype == CXL_DTYPE_BF16)
+    return pack_to(src, src_dtype, item_stride, row_stride, items, n, n_pad, D, reinterpret_cast<__nv_bfloat16*>(dst),
+                   static_cast<unsigned>(blocks), stream);
+  if (dst_dtype == CXL_DTYPE_F16)
+    return pack_to(src, src_dtype, item_stride, row_stride, items, n, n_pad, D, reinterpret_cast<__half*>(dst),
+                   static_cast<unsigned>(blocks), stream);
+  return CXL_ERR_INVALID_ARG;
+}
+
+int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
+              int D, void* dst, cudaStream_t stream) {
+  return pack_operand(src, src_dtype, item_stride, row_stride, items, n, n_pad, D, dst, CXL_DTYPE_BF16, stream);
 }
 
 // w = dS * g / (cnt + 1e-8)   (masked mean, loss.py:40-44)   or   dS * g / T   (plain mean, model.py:628)

@@ -12,7 +12,7 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
-from ._lib import CXL_DTYPE_BF16, CXL_DTYPE_F32, CXL_MEAN_MASKED, CXL_MEAN_PLAIN, check
+from ._lib import CXL_DTYPE_BF16, CXL_DTYPE_F16, CXL_DTYPE_F32, CXL_MEAN_MASKED, CXL_MEAN_PLAIN, check
 
 MASKED = CXL_MEAN_MASKED
 MEAN = CXL_MEAN_PLAIN
@@ -20,6 +20,11 @@ MEAN = CXL_MEAN_PLAIN
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
+
+
+_PREC_DT = {"bf16": CXL_DTYPE_BF16, "fp16": CXL_DTYPE_F16, "fp32": CXL_DTYPE_F32}
+_PREC_TORCH = {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}
+_TORCH_DT = {torch.float32: CXL_DTYPE_F32, torch.bfloat16: CXL_DTYPE_BF16, torch.float16: CXL_DTYPE_F16}
 
 
 def _stream() -> int:
@@ -53,26 +58,26 @@ class CudaKernels:
 
     # ---- layout helpers ---------------------------------------------------------------------
     def img_row_stride(self, P: int, prec: str) -> int:
-        return int(self.lib.cxl_img_row_stride(P)) if prec == "bf16" else P
+        return int(self.lib.cxl_img_row_stride(P)) if prec != "fp32" else P
 
     def prepare(self, x: torch.Tensor, n_pad: int, prec: str) -> torch.Tensor:
-        """[N,n,D] features -> kernel operand: bf16 [N,n_pad,D] (tensor-core path) or fp32 [N,n,D]."""
+        """[N,n,D] features -> kernel operand: bf16 / fp16 [N,n_pad,D] (tensor-core path) or fp32 [N,n,D]."""
         dev = _require_cuda(x)
         N, n, D = x.shape
         x = x.detach()
         if prec == "fp32":
             return x.float().contiguous()
-        if x.dtype == torch.bfloat16 and x.is_contiguous() and n_pad == n:
+        op_dt = _PREC_TORCH[prec]
+        if x.dtype == op_dt and x.is_contiguous() and n_pad == n:
             return x
-        if x.dtype not in (torch.float32, torch.bfloat16):
+        if x.dtype not in _TORCH_DT:
             x = x.float()
         if x.stride(2) != 1:
             x = x.contiguous()
-        out = torch.empty((N, n_pad, D), dtype=torch.bfloat16, device=dev)
+        out = torch.empty((N, n_pad, D), dtype=op_dt, device=dev)
         with torch.cuda.device(dev):
-            check(self.lib.cxl_pack_bf16(_ptr(x), CXL_DTYPE_F32 if x.dtype == torch.float32 else CXL_DTYPE_BF16,
-                                         x.stride(0), x.stride(1), N, n, n_pad, D, _ptr(out), _stream()),
-                  "cxl_pack_bf16")
+            check(self.lib.cxl_pack_operand(_ptr(x), _TORCH_DT[x.dtype], x.stride(0), x.stride(1), N, n, n_pad, D,
+                                            _ptr(out), _PREC_DT[prec], _stream()), "cxl_pack_operand")
         return out
 
     def _alloc_argmax(self, Bt: int, Bi: int, T: int, P: int, dev) -> torch.Tensor:
@@ -101,8 +106,7 @@ class CudaKernels:
         cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if mean_mode == MASKED else None
         argmax = self._alloc_argmax(Bt, Bi, T, P, dev) if save_argmax else None
         with torch.cuda.device(dev):
-            check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D,
-                                          CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32, mean_mode,
+            check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, _PREC_DT[prec], mean_mode,
                                           _ptr(S), _ptr(cnt), _ptr(argmax), _stream()), "cxl_maxsim_fwd")
         return S, cnt, argmax
 
@@ -129,7 +133,7 @@ class CudaKernels:
         dtxt = torch.empty((Bt, T, D), dtype=torch.float32, device=dev) if need_txt else None
         dimg = torch.empty((n_img, P, D), dtype=torch.float32, device=dev) if need_img else None
         img_shard = img_op[k_off:k_off + n_img]
-        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        dt = _PREC_DT[prec]
         with torch.cuda.device(dev):
             if generic:
                 check(self.lib.cxl_maxsim_bwd_generic(_ptr(txt_op), _ptr(img_shard), _ptr(argmax), _ptr(w), Bt, n_img,
@@ -149,10 +153,12 @@ class CudaKernels:
         return dtxt, dimg
 
     def maxsim_bwd_shard(self, txt_op, img_sh, arg_sh, w, k_off: int, T: int, P: int, prec: str,
-                         dtxt: Optional[torch.Tensor] = None, accumulate_txt: bool = False, need_img: bool = True):
+                         dtxt: Optional[torch.Tensor] = None, accumulate_txt: bool = False, need_img: bool = True,
+                         w_scale: Optional[torch.Tensor] = None):
         """K2 for ONE SHARD of the images with shard-local operands (cxl_maxsim_bwd_shard): img_sh [n,p_stride,D] and
         arg_sh [n, ld] are the shard's own buffers, w [Bt, ld_pairs] covers all images and the shard is its columns
         [k_off, k_off+n).  `dtxt` [Bt,T,D] fp32 (optional) is overwritten, or added to when accumulate_txt.
+        w_scale: optional device pair [s, 1/s] (power of two) applied to the 16-bit copy of w inside the kernels.
         Returns the shard's dImg partial [n,P,D] fp32 (None unless need_img)."""
         dev = _require_cuda(txt_op, img_sh, arg_sh, w, dtxt)
         Bt, D = txt_op.shape[0], txt_op.shape[2]
@@ -160,28 +166,29 @@ class CudaKernels:
         assert w.is_contiguous() and w.dtype == torch.float32 and img_sh.is_contiguous() and arg_sh.is_contiguous()
         assert dtxt is None or (dtxt.is_contiguous() and dtxt.dtype == torch.float32)
         dimg = torch.empty((n, P, D), dtype=torch.float32, device=dev) if need_img else None
-        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        dt = _PREC_DT[prec]
         with torch.cuda.device(dev):
             nws = int(self.lib.cxl_maxsim_bwd_workspace_bytes(Bt, n, T, P, D, dt)) if need_img else 0
             ws = torch.empty(nws, dtype=torch.uint8, device=dev) if nws > 0 else None
             check(self.lib.cxl_maxsim_bwd_shard(_ptr(txt_op), _ptr(img_sh), _ptr(arg_sh), _ptr(w), Bt, n, T, P, D, dt,
                                                 w.shape[1], k_off, _ptr(dtxt), 1 if accumulate_txt else 0, _ptr(dimg),
-                                                0, _ptr(ws), nws, _stream()), "cxl_maxsim_bwd_shard")
+                                                0, _ptr(w_scale), _ptr(ws), nws, _stream()), "cxl_maxsim_bwd_shard")
         return dimg
 
     def maxsim_bwd_dtxt_rows_shard(self, img_sh, arg_sh, w, k_off: int, Bt_total: int, m0: int, m_cnt: int, T: int,
-                                   P: int, prec: str, dtxt: torch.Tensor, accumulate_txt: bool):
+                                   P: int, prec: str, dtxt: torch.Tensor, accumulate_txt: bool,
+                                   w_scale: Optional[torch.Tensor] = None):
         """dTxt of texts m0..m0+m_cnt-1 against one shard of the images (shard-local img / argmax), into dtxt
         [m_cnt,T,D] fp32 (overwritten or accumulated)."""
         dev = _require_cuda(img_sh, arg_sh, w, dtxt)
         D = img_sh.shape[2]
         assert w.is_contiguous() and w.dtype == torch.float32 and w.shape[0] == Bt_total
         assert dtxt.is_contiguous() and dtxt.dtype == torch.float32
-        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        dt = _PREC_DT[prec]
         with torch.cuda.device(dev):
             check(self.lib.cxl_maxsim_bwd_dtxt_rows_shard(_ptr(img_sh), _ptr(arg_sh), _ptr(w), Bt_total, m0, m_cnt,
                                                           img_sh.shape[0], T, P, D, dt, w.shape[1], k_off, _ptr(dtxt),
-                                                          1 if accumulate_txt else 0, _stream()),
+                                                          1 if accumulate_txt else 0, _ptr(w_scale), _stream()),
                   "cxl_maxsim_bwd_dtxt_rows_shard")
         return dtxt
 
@@ -193,7 +200,7 @@ class CudaKernels:
         D = img_op.shape[2]
         assert w.is_contiguous() and w.dtype == torch.float32 and w.shape[0] == Bt_total
         dtxt = torch.empty((m_cnt, T, D), dtype=torch.float32, device=dev)
-        dt = CXL_DTYPE_BF16 if prec == "bf16" else CXL_DTYPE_F32
+        dt = _PREC_DT[prec]
         with torch.cuda.device(dev):
             check(self.lib.cxl_maxsim_bwd_dtxt_rows(_ptr(img_op), _ptr(argmax), _ptr(w), Bt_total, m0, m_cnt,
                                                     img_op.shape[0], T, P, D, dt, w.shape[1], 0, _ptr(dtxt),
@@ -238,11 +245,9 @@ class CudaKernels:
     # ---- producer side: L2 normalise + operand cast -----------------------------------
     @staticmethod
     def _dt(t: torch.Tensor) -> int:
-        if t.dtype == torch.float32:
-            return CXL_DTYPE_F32
-        if t.dtype == torch.bfloat16:
-            return CXL_DTYPE_BF16
-        raise RuntimeError(f"colxlip_b200: unsupported dtype {t.dtype} (float32 / bfloat16 only)")
+        if t.dtype in _TORCH_DT:
+            return _TORCH_DT[t.dtype]
+        raise RuntimeError(f"colxlip_b200: unsupported dtype {t.dtype} (float32 / bfloat16 / float16 only)")
 
     def l2norm_fwd(self, x: torch.Tensor, out_dtype: torch.dtype, save_inv: bool = True):
         """x [..., D] (f32|bf16, contiguous) -> (y [..., D] out_dtype, inv_norm [rows] f32 or None)."""

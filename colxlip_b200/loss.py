@@ -28,15 +28,16 @@ except ImportError:  # pragma: no cover
 
 from .kernels import MASKED, MEAN, default_kernels
 
-# "auto": tensor-core bf16 path under autocast or for 16-bit inputs, fp32 SIMT path for fp32 inputs
-# outside autocast (what torch.einsum would do at loss.py:34).  "bf16"/"fp32" force one path.
+# "auto": tensor-core path in the 16-bit dtype torch.einsum would use at loss.py:34 -- the autocast dtype under CUDA
+# autocast (bf16, or fp16 for the reference's `--precision amp`, colxlip.sh:53 / train.py:131-134), else the
+# inputs' own 16-bit dtype; fp32 SIMT path for fp32 inputs outside autocast.  "bf16"/"fp16"/"fp32" force one path.
 _PRECISION = os.environ.get("COLXLIP_B200_PRECISION", "auto")
 
 
 def set_precision(mode: str) -> None:
     global _PRECISION
-    if mode not in ("auto", "bf16", "fp32"):
-        raise ValueError("precision must be auto|bf16|fp32")
+    if mode not in ("auto", "bf16", "fp16", "fp32"):
+        raise ValueError("precision must be auto|bf16|fp16|fp32")
     _PRECISION = mode
 
 
@@ -44,16 +45,33 @@ def get_precision() -> str:
     return _PRECISION
 
 
+def _auto_precision(*tensors: torch.Tensor) -> str:
+    t0 = tensors[0]
+    if t0.is_cuda and torch.is_autocast_enabled("cuda"):
+        return "fp16" if torch.get_autocast_dtype("cuda") == torch.float16 else "bf16"
+    if all(t.dtype == torch.float16 for t in tensors):
+        return "fp16"
+    if all(t.dtype in (torch.bfloat16, torch.float16) for t in tensors):
+        return "bf16"                                   # mixed 16-bit inputs: torch promotes bf16 x fp16 to fp32; bf16 operands here
+    return "fp32"
+
+
 def _select_precision(*tensors: torch.Tensor) -> str:
     D = tensors[0].shape[-1]
     mode = _PRECISION
     if mode == "auto":
-        autocast = torch.is_autocast_enabled("cuda") if tensors[0].is_cuda else False
-        low = all(t.dtype in (torch.bfloat16, torch.float16) for t in tensors)
-        mode = "bf16" if (autocast or low) else "fp32"
-    if mode == "bf16" and D % 64 != 0:
+        mode = _auto_precision(*tensors)
+    if mode in ("bf16", "fp16") and D % 64 != 0:
         mode = "fp32"  # the tcgen05 kernel tiles D in 64-wide swizzled blocks; fp32 SIMT kernel covers the rest
     return mode
+
+
+def _w_scale_from_bound(bound: torch.Tensor) -> torch.Tensor:
+    """[s, 1/s] on the device, s = the power of two that puts `bound` (an upper bound of |w|, a device scalar) at
+    2^15: fp16 pair weights then use the top of their range whatever the loss scale is (no host sync)."""
+    e = torch.ceil(torch.log2(bound.float().abs().clamp_min(1e-30)))
+    s = torch.exp2(15.0 - e).reshape(1)
+    return torch.cat([s, 1.0 / s]).contiguous()
 
 
 def _check_tokens(img: torch.Tensor, txt: torch.Tensor) -> None:
@@ -88,7 +106,14 @@ class _MaxSimFn(torch.autograd.Function):
         txt_op, img_op, argmax, cnt = ctx.saved_tensors
         need_img, need_txt = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
         w = k.pair_weights(dS, cnt, T, mean_mode)
-        dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=need_txt, need_img=need_img)
+        if prec == "fp16":
+            # fp16 pair weights: scale by the power of two that puts max|w| at 2^15, undone exactly at the store
+            D = txt_op.shape[2]
+            dtxt = torch.empty((txt_op.shape[0], T, D), dtype=torch.float32, device=txt_op.device) if need_txt else None
+            dimg = k.maxsim_bwd_shard(txt_op, img_op, argmax, w, 0, T, P, prec, dtxt=dtxt, need_img=need_img,
+                                      w_scale=_w_scale_from_bound(w.abs().amax()))
+        else:
+            dtxt, dimg = k.maxsim_bwd(txt_op, img_op, argmax, w, T, P, prec, need_txt=need_txt, need_img=need_img)
         return (dimg.to(img_dt) if need_img else None, dtxt.to(txt_dt) if need_txt else None, None, None, None, None)
 
 
@@ -233,10 +258,12 @@ class _FwdState:
 
 
 def _round_like_gemm_input(x: torch.Tensor, prec: str) -> torch.Tensor:
-    """fp32 copy of the global features as the GEMM sees them (bf16-rounded on the bf16 path)."""
+    """fp32 copy of the global features as the GEMM sees them (rounded to the operand dtype on the 16-bit paths)."""
     x = x.detach()
     if prec == "bf16":
         return x.to(torch.bfloat16).float()
+    if prec == "fp16":
+        return x.to(torch.float16).float()
     return x.float()
 
 
@@ -378,6 +405,8 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
     dscale = dscale_t + dscale_g
     if W > 1:
         dist.all_reduce(dscale, group=group)
+    # fp16 operands: |w| <= 2 |coef_t| scale / 2B (softmax terms <= 1, cnt >= 1): that bound goes to 2^15 (see header)
+    w_scale = _w_scale_from_bound(coef_t * scale / float(b * W)) if prec == "fp16" else None
 
     mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
     d_txt = dG @ st.g_img if need[1] else None
@@ -404,7 +433,8 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
             for lo in range(0, b, chunk):
                 hi = min(b, lo + chunk)
                 part = k.maxsim_bwd_shard(txt_op, img_sh[lo:hi], k.argmax_images(arg_sh, lo, hi), w, r * b + lo, T, P,
-                                          prec, dtxt=dtxt_tok, accumulate_txt=not (r == 0 and first), need_img=need[2])
+                                          prec, dtxt=dtxt_tok, accumulate_txt=not (r == 0 and first), need_img=need[2],
+                                          w_scale=w_scale)
                 first = False
                 if need[2]:
                     if W == 1:
@@ -416,12 +446,13 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
             # gradient-accumulation call (train.py:166-183): only samples lo_t..hi_t-1 of every rank's batch carry
             # gradient, so K2 runs on that slice alone -- 1/accum_freq of the items
             if need[3]:
-                k.maxsim_bwd_dtxt_rows_shard(img_sh, arg_sh, w, r * b, b, lo_t, n_t, T, P, prec, dtxt_tok, r > 0)
+                k.maxsim_bwd_dtxt_rows_shard(img_sh, arg_sh, w, r * b, b, lo_t, n_t, T, P, prec, dtxt_tok, r > 0,
+                                             w_scale=w_scale)
             if need[2]:
                 for lo in range(lo_t, hi_t, chunk):
                     hi = min(hi_t, lo + chunk)
                     part = k.maxsim_bwd_shard(txt_op, img_sh[lo:hi], k.argmax_images(arg_sh, lo, hi), w, r * b + lo,
-                                              T, P, prec, need_img=True)
+                                              T, P, prec, need_img=True, w_scale=w_scale)
                     if W == 1:
                         out_ref[0] = part if (lo == lo_t and hi == hi_t) else _place(out_ref, part, lo - lo_t, hi - lo_t,
                                                                                      (n_t, P, D))
@@ -687,9 +718,7 @@ class ColClipLoss(nn.Module):
 def _select_global_precision(*tensors: torch.Tensor) -> str:
     mode = _PRECISION
     if mode == "auto":
-        autocast = torch.is_autocast_enabled("cuda") if tensors[0].is_cuda else False
-        low = all(t.dtype in (torch.bfloat16, torch.float16) for t in tensors)
-        mode = "bf16" if (autocast or low) else "fp32"
+        mode = _auto_precision(*tensors)
     return mode
 
 

@@ -19,8 +19,10 @@ class _L2NormFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, out_dtype, kernels):
         xc = x.detach()
-        if xc.dtype not in (torch.float32, torch.bfloat16):
+        if xc.dtype not in (torch.float32, torch.bfloat16, torch.float16):
             xc = xc.float()
+        if xc.dtype != torch.float32 and out_dtype not in (xc.dtype, torch.float32):
+            xc = xc.float()                            # bf16 <-> fp16: through fp32 (no such kernel pair)
         y, inv = kernels.l2norm_fwd(xc.contiguous(), out_dtype, save_inv=x.requires_grad)
         if x.requires_grad:
             ctx.save_for_backward(y, inv)
@@ -32,9 +34,11 @@ class _L2NormFn(torch.autograd.Function):
     def backward(ctx, g):
         kernels, dt = ctx.meta
         y, inv = ctx.saved_tensors
-        if g.dtype not in (torch.float32, torch.bfloat16):
+        if g.dtype != torch.float32 and g.dtype != y.dtype:
             g = g.float()
-        out_dt = dt if dt in (torch.float32, torch.bfloat16) else torch.float32
+        out_dt = dt if dt in (torch.float32, torch.bfloat16, torch.float16) else torch.float32
+        if y.dtype == torch.float32 and g.dtype == torch.float16:
+            g = g.float()
         return kernels.l2norm_bwd(y, g.contiguous(), inv, out_dt).to(dt), None, None
 
 
@@ -42,16 +46,20 @@ def normalize_tokens(x, out_dtype=None, kernels=None):
     """F.normalize(x, dim=-1) as the reference applies it to the token / global embeddings
     (model.py:551-554, 605-607), fused with the cast to the dtype the MaxSim kernels consume.
 
-    out_dtype=None: bfloat16 under CUDA autocast or for bf16 inputs (what torch.einsum at loss.py:34 would cast
-    its operand to), else x.dtype.  A bf16 result goes into ColClipLoss / compute_colbert_similarity without a
+    out_dtype=None: the autocast dtype under CUDA autocast (bfloat16, or float16 for `--precision amp`), the
+    input's dtype for 16-bit inputs (what torch.einsum at loss.py:34 would cast its operand to), else float32.
+    A 16-bit result goes into ColClipLoss / compute_colbert_similarity without a
     further pack pass, and into the feature all-gather at half the fp32 bytes.  x: [..., D], D % 8 == 0."""
     if x.dim() < 1 or x.shape[-1] % 8 != 0:
         raise ValueError("normalize_tokens needs an embedding dimension that is a multiple of 8 (16-byte row accesses)")
     k = kernels if kernels is not None else default_kernels()
     if out_dtype is None:
-        autocast = x.is_cuda and torch.is_autocast_enabled("cuda")
-        bf = x.dtype == torch.bfloat16 or (autocast and torch.get_autocast_dtype("cuda") == torch.bfloat16)
-        out_dtype = torch.bfloat16 if bf else (x.dtype if x.dtype == torch.float32 else torch.float32)
+        if x.is_cuda and torch.is_autocast_enabled("cuda"):
+            out_dtype = torch.get_autocast_dtype("cuda")
+        elif x.dtype in (torch.bfloat16, torch.float16):
+            out_dtype = x.dtype
+        else:
+            out_dtype = torch.float32
     return _L2NormFn.apply(x, out_dtype, k)
 
 

@@ -34,6 +34,7 @@ extern "C" {
 
 #define CXL_DTYPE_F32 0
 #define CXL_DTYPE_BF16 1
+#define CXL_DTYPE_F16 2 /* fp16 operands (the reference's `--precision amp`): same kernels, kind::f16 with F16 formats */
 
 #define CXL_MEAN_MASKED 0 /* loss.py:38-44  sum / (count(max != 0) + 1e-8) */
 #define CXL_MEAN_PLAIN 1  /* model.py:628   mean over all T tokens          */
@@ -60,6 +61,10 @@ long long cxl_argmax_ld(int Bt, int T);
  */
 int cxl_pack_bf16(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride,
                   int items, int n, int n_pad, int D, void* dst, void* stream);
+/* Same with the operand dtype chosen by the caller: dst_dtype CXL_DTYPE_BF16 or CXL_DTYPE_F16 (fp16 autocast,
+ * train.py:131-134 with --precision amp); src f32 / bf16 / f16. */
+int cxl_pack_operand(const void* src, int src_dtype, long long src_item_stride, long long src_row_stride,
+                     int items, int n, int n_pad, int D, void* dst, int dst_dtype, void* stream);
 
 /*
  * MaxSim forward.  Replaces compute_colbert_similarity (loss.py:20-46) when
@@ -140,14 +145,18 @@ int cxl_maxsim_bwd_dtxt_rows(const void* img, const void* argmax, const float* w
  *          continue the same chain of additions, so the result has the bits of one call over all images.
  *   dimg   [Bi,P,D] or NULL (the shard's partial), accumulate_img as above.
  * A sub-range [lo, lo+n) of a shard is the same call with img / argmax / dimg advanced by lo images and k_off + lo.
+ *   w_scale_dev  NULL, or a device pair {s, 1/s} with s a power of two: the streaming kernels multiply with a 16-bit
+ *          copy of w (bf16, or fp16 for CXL_DTYPE_F16 operands); s is applied before that rounding and undone exactly
+ *          at the store, which keeps fp16 weights inside their range whatever the loss scale (GradScaler) is.
  */
 int cxl_maxsim_bwd_shard(const void* txt, const void* img, const void* argmax, const float* w, int Bt, int Bi, int T,
                          int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt, int accumulate_txt,
-                         float* dimg, int accumulate_img, void* ws, size_t ws_bytes, void* stream);
+                         float* dimg, int accumulate_img, const float* w_scale_dev, void* ws, size_t ws_bytes,
+                         void* stream);
 /* cxl_maxsim_bwd_dtxt_rows for one shard with shard-local img / argmax (see above), optionally accumulating. */
 int cxl_maxsim_bwd_dtxt_rows_shard(const void* img, const void* argmax, const float* w, int Bt_total, int m0, int m_cnt,
                                    int Bi, int T, int P, int D, int dtype, int ld_pairs, int k_off, float* dtxt,
-                                   int accumulate_txt, void* stream);
+                                   int accumulate_txt, const float* w_scale_dev, void* stream);
 
 /*
  * Symmetric InfoNCE over a [B_loc, B] block of UNSCALED logits (rows = texts row0..row0+B_loc,

@@ -21,6 +21,8 @@ class TorchRefKernels:
         x = x.detach()
         if prec == "bf16":
             return x.to(torch.bfloat16).float().contiguous()
+        if prec == "fp16":
+            return x.to(torch.float16).float().contiguous()
         return x.float().contiguous()
 
     def maxsim_fwd(self, txt_op, img_op, T, P, prec, mean_mode, save_argmax):
@@ -61,7 +63,7 @@ class TorchRefKernels:
         return dtxt, dimg
 
     def maxsim_bwd_shard(self, txt_op, img_sh, arg_sh, w, k_off, T, P, prec, dtxt=None, accumulate_txt=False,
-                         need_img=True):
+                         need_img=True, w_scale=None):
         """arg_sh: the shard's argmax [Bt, n, T] (what maxsim_fwd(txt_op, img_sh) returned)."""
         Bt, _, D = txt_op.shape
         n = img_sh.shape[0]
@@ -79,7 +81,8 @@ class TorchRefKernels:
                 dimg[k].index_add_(0, arg_sh[:, k].reshape(-1), contrib)
         return dimg
 
-    def maxsim_bwd_dtxt_rows_shard(self, img_sh, arg_sh, w, k_off, Bt_total, m0, m_cnt, T, P, prec, dtxt, accumulate_txt):
+    def maxsim_bwd_dtxt_rows_shard(self, img_sh, arg_sh, w, k_off, Bt_total, m0, m_cnt, T, P, prec, dtxt, accumulate_txt,
+                                   w_scale=None):
         if not accumulate_txt:
             dtxt.zero_()
         for k in range(img_sh.shape[0]):
