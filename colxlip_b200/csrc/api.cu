@@ -51,6 +51,10 @@ int pack_bf16(const void* src, int src_dtype, long long item_stride, long long r
               int D, void* dst, cudaStream_t stream);
 int pack_operand(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n,
                  int n_pad, int D, void* dst, int dst_dtype, cudaStream_t stream);
+int gemm_nt_tc(const void* A, const void* B, int M, int N, int K, float* C, long long ldc, int f16, cudaStream_t stream);
+int cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtype, const float* scale, cudaStream_t stream);
+int poison_nonfinite(const void* txt, const void* img, int Bt, int Bi, int T, int p_stride, int D, int dtype, float* S,
+                     cudaStream_t stream);
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
                    const int* target, int* rank_out, cudaStream_t stream);
 
@@ -128,12 +132,16 @@ int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int 
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long ld_arg = cxl_argmax_ld(Bt, T);
   if (dtype == CXL_DTYPE_BF16 || dtype == CXL_DTYPE_F16)
-    return maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0,
-                         dtype == CXL_DTYPE_F16, st);
-  if (dtype == CXL_DTYPE_F32)
-    return maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
-                          cnt, argmax, ld_arg, st);
-  return CXL_ERR_INVALID_ARG;
+    rc = maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0,
+                       dtype == CXL_DTYPE_F16, st);
+  else if (dtype == CXL_DTYPE_F32)
+    rc = maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
+                        cnt, argmax, ld_arg, st);
+  else
+    return CXL_ERR_INVALID_ARG;
+  if (rc != CXL_OK) return rc;
+  // torch.max propagates NaN, the epilogue's running max does not: scores of texts / images with a non-finite element -> NaN
+  return poison_nonfinite(txt, img, Bt, Bi, T, dtype == CXL_DTYPE_F32 ? P : img_row_stride(P), D, dtype, S, st);
 }
 
 int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev, int mean_mode, int T, long long n,
@@ -267,6 +275,22 @@ int cxl_l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   return l2norm_bwd(y, y_dtype, g, g_dtype, inv_norm, rows, D, dx, dx_dtype, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_gemm_nt(const void* A, const void* B, int M, int N, int K, int dtype, float* C, long long ldc, void* stream) {
+  if (!A || !B || !C) return CXL_ERR_INVALID_ARG;
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F16) return CXL_ERR_INVALID_ARG;
+  if ((reinterpret_cast<uintptr_t>(A) | reinterpret_cast<uintptr_t>(B)) & 15) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return gemm_nt_tc(A, B, M, N, K, C, ldc, dtype == CXL_DTYPE_F16, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtype, const float* scale_dev, void* stream) {
+  if (!X || (!Y && !Yt)) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return cast_transpose(X, R, C, Y, Yt, dtype, scale_dev, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,

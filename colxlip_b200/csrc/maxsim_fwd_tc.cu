@@ -49,6 +49,9 @@ struct FwdTcParams {
   void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
   long long ld_arg;
   float* dbg;            // debug: raw accumulators of (unit 0, first tile) as [128, n_tile], or null
+  float* raw_c;          // plain GEMM mode (cxl_gemm_nt): C[rows_a, raw_n] = A * B^T, every accumulator stored; or null
+  long long raw_ldc;     // row pitch of C in elements
+  int raw_n;             // columns of C (rows of B)
 #ifdef CXL_EXPERIMENTS
   int exp_mode;          // timing experiments, compiled only with -DCXL_EXPERIMENTS (env CXL_K1_EXP): bit0 = skip the
                          // epilogue scan (WRONG results); release builds carry no such switch
@@ -275,6 +278,40 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
           }
         }
 
+        if (p.raw_c != nullptr) {
+          // plain GEMM: tile j covers C columns [j * p_stride, j * p_stride + n_tile); lane = row, 16 columns per tcgen05.ld
+          const int col0 = j * p.p_stride;
+          float* crow = p.raw_c + static_cast<size_t>(R) * p.raw_ldc;
+          const bool vec_ok = (p.raw_ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(p.raw_c) & 15) == 0;
+          uint32_t va[16], vb[16];
+          tmem_ld16(tbase, va);
+          for (int c0 = 0; c0 < p.n_tile; c0 += 16) {
+            tmem_wait_ld16(va);
+#pragma unroll
+            for (int jj = 0; jj < 16; ++jj) vb[jj] = va[jj];
+            if (c0 + 16 < p.n_tile) tmem_ld16(tbase + c0 + 16, va);     // next chunk in flight while this one is stored
+            const int cc = col0 + c0;
+            if (valid && cc < p.raw_n) {
+              if (vec_ok && cc + 16 <= p.raw_n) {
+#pragma unroll
+                for (int q4 = 0; q4 < 4; ++q4)
+                  *reinterpret_cast<float4*>(crow + cc + 4 * q4) =
+                      make_float4(__uint_as_float(vb[4 * q4]), __uint_as_float(vb[4 * q4 + 1]),
+                                  __uint_as_float(vb[4 * q4 + 2]), __uint_as_float(vb[4 * q4 + 3]));
+              } else {
+#pragma unroll
+                for (int jj = 0; jj < 16; ++jj)
+                  if (cc + jj < p.raw_n) crow[cc + jj] = __uint_as_float(vb[jj]);
+              }
+            }
+          }
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(smem_u32(&bars->tmem_empty[buf]));
+          buf ^= 1;
+          if (buf == 0) acc_phase ^= 1;
+          continue;
+        }
         const int qoff = part * p.part_cols;
         const int ncols = (p.parts == 1) ? p.P : min(p.part_cols, p.P - qoff);
         const int nchunks = (ncols + 15) >> 4;
@@ -814,6 +851,58 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   CXL_CUDA_CHECK(cudaGetLastError());
 
   return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);
+}
+
+// ------------------------------------------------------------------------------------------------
+// Plain NT GEMM on the same pipeline: C[M,N] (f32) = A[M,K] * B[N,K]^T, 16-bit operands (bf16 / fp16), fp32 accumulate.
+// Serves the global-embedding half of the losses (loss.py:252-253, 132-160): logits [b,B] = txt [b,D] x img [B,D]^T and
+// the two gradient GEMMs of their backward.  M tile 128 rows, N tile 256 rows of B, K in 64-wide blocks; the A tile
+// stays resident when K is small (the logits GEMM), is streamed with B otherwise (the gradient GEMMs, K = batch).
+int gemm_nt_tc(const void* A, const void* B, int M, int N, int K, float* C, long long ldc, int f16, cudaStream_t stream) {
+  if (K % kBlockK != 0 || K < kBlockK || M <= 0 || N <= 0 || ldc < N) return CXL_ERR_UNSUPPORTED;
+  FwdTcParams p;
+  memset(&p, 0, sizeof(p));
+  p.Bt = M; p.T = 1; p.rows_a = M; p.D = K; p.num_kb = K / kBlockK;
+  p.P = 256; p.p_stride = 256; p.ipt = 1; p.parts = 1; p.part_cols = 256; p.n_tile = 256;
+  p.Bi = (N + 255) / 256;
+  p.f16 = f16 ? 1 : 0;
+  p.total_n_tiles = p.Bi;
+  p.num_m_tiles = (M + kBlockM - 1) / kBlockM;
+  p.b_block_bytes = p.n_tile * kBlockK * 2;
+  p.raw_c = C; p.raw_ldc = ldc; p.raw_n = N;
+  int dev = 0, max_smem = 0;
+  CXL_CUDA_CHECK(cudaGetDevice(&dev));
+  CXL_CUDA_CHECK(cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev));
+  const int overhead = 1024 + static_cast<int>(sizeof(FwdTcBarriers)) + 64;
+  const int b_stage = p.b_block_bytes;                    // 32 KB, already a multiple of 1024
+  p.a_resident = 1;
+  int stages = (max_smem - overhead - p.num_kb * kABlockBytes) / b_stage;
+  if (stages < 3) {
+    p.a_resident = 0;
+    p.stage_bytes = b_stage + kABlockBytes;
+    stages = (max_smem - overhead) / p.stage_bytes;
+  } else {
+    p.stage_bytes = b_stage;
+  }
+  p.num_stages = stages > kMaxStages ? kMaxStages : stages;
+  const int smem_bytes = overhead + (p.a_resident ? p.num_kb * kABlockBytes : 0) + p.num_stages * p.stage_bytes;
+  const int sms = num_sms();
+  // units = (m tile, chunk of n tiles); whole sweeps per unit when there are enough m tiles, else split the sweep
+  long long tpu = p.total_n_tiles;
+  while (tpu > 1 && static_cast<long long>(p.num_m_tiles) * ((p.total_n_tiles + tpu - 1) / tpu) < 2LL * sms) tpu = (tpu + 1) / 2;
+  p.tiles_per_unit = static_cast<int>(tpu);
+  const int chunks = (p.total_n_tiles + p.tiles_per_unit - 1) / p.tiles_per_unit;
+  p.num_units = chunks * p.num_m_tiles;
+  CUtensorMap tmA, tmB;
+  int rc = make_tmap(&tmA, A, M, K, kBlockM, p.f16);
+  if (rc != CXL_OK) return rc;
+  rc = make_tmap(&tmB, B, N, K, p.n_tile, p.f16);
+  if (rc != CXL_OK) return rc;
+  CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+  const int grid = p.num_units < sms ? p.num_units : sms;
+  maxsim_fwd_tc_kernel<<<grid, kThreads, smem_bytes, CXL_COUNTED(stream)>>>(tmA, tmB, p);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
 }
 
 }  // namespace cxl

@@ -200,4 +200,108 @@ int rank_of_target(const float* scores, long long row_stride, long long col_stri
   return CXL_OK;
 }
 
+// X [R,C] f32 -> Y [R,C] and Yt [C,R] in bf16 / fp16 (either output may be null): the 16-bit copies of dL/dlogits the two
+// gradient GEMMs of the global-embedding loss consume (the reference's autocast backward multiplies a 16-bit dlogits,
+// loss.py:252-253).  32 x 32 tiles through shared memory: both the row-major and the transposed store are coalesced.
+template <typename O>
+__global__ void __launch_bounds__(256) cast_transpose_kernel(const float* __restrict__ X, int R, int C,
+                                                             O* __restrict__ Y, O* __restrict__ Yt,
+                                                             const float* __restrict__ scale) {
+  __shared__ float tile[32][33];
+  const float sc = scale != nullptr ? __ldg(scale) : 1.f;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;          // 32 x 8 threads
+  const int c0 = blockIdx.x * 32, r0 = blockIdx.y * 32;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int r = r0 + ty + 8 * i, c = c0 + tx;
+    float v = 0.f;
+    if (r < R && c < C) v = X[static_cast<size_t>(r) * C + c] * sc;
+    tile[ty + 8 * i][tx] = v;
+    if (Y != nullptr && r < R && c < C) Y[static_cast<size_t>(r) * C + c] = static_cast<O>(v);
+  }
+  __syncthreads();
+  if (Yt != nullptr) {
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+      const int c = c0 + ty + 8 * i, r = r0 + tx;
+      if (r < R && c < C) Yt[static_cast<size_t>(c) * R + r] = static_cast<O>(tile[tx][ty + 8 * i]);
+    }
+  }
+}
+
+int cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtype, const float* scale, cudaStream_t stream) {
+  if (R <= 0 || C <= 0) return CXL_ERR_INVALID_ARG;
+  dim3 grid((C + 31) / 32, (R + 31) / 32);
+  if (grid.y > 65535) return CXL_ERR_UNSUPPORTED;
+  if (dtype == CXL_DTYPE_BF16)
+    cast_transpose_kernel<__nv_bfloat16><<<grid, 256, 0, CXL_COUNTED(stream)>>>(X, R, C, static_cast<__nv_bfloat16*>(Y),
+                                                                                static_cast<__nv_bfloat16*>(Yt), scale);
+  else if (dtype == CXL_DTYPE_F16)
+    cast_transpose_kernel<__half><<<grid, 256, 0, CXL_COUNTED(stream)>>>(X, R, C, static_cast<__half*>(Y),
+                                                                         static_cast<__half*>(Yt), scale);
+  else
+    return CXL_ERR_INVALID_ARG;
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
+// NaN propagation of torch.max (loss.py:35): the K1 epilogues keep a running maximum with `x > best`, which drops NaN
+// similarities instead of propagating them.  A NaN / Inf similarity can only come from a NaN / Inf operand element, so
+// the operands are scanned once (HBM speed) and every score of a text / an image that holds a non-finite element is
+// set to NaN: the loss and the gradients of that step become non-finite, which is what AMP's GradScaler looks for.
+template <typename T> __device__ __forceinline__ bool nonfinite16(uint4 v);
+template <> __device__ __forceinline__ bool nonfinite16<__nv_bfloat16>(uint4 v) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  bool bad = false;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) bad |= ((w[i] & 0x7F80u) == 0x7F80u) || ((w[i] & 0x7F800000u) == 0x7F800000u);
+  return bad;
+}
+template <> __device__ __forceinline__ bool nonfinite16<__half>(uint4 v) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  bool bad = false;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) bad |= ((w[i] & 0x7C00u) == 0x7C00u) || ((w[i] & 0x7C000000u) == 0x7C000000u);
+  return bad;
+}
+template <> __device__ __forceinline__ bool nonfinite16<float>(uint4 v) {
+  const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+  bool bad = false;
+#pragma unroll
+  for (int i = 0; i < 4; ++i) bad |= (w[i] & 0x7F800000u) == 0x7F800000u;
+  return bad;
+}
+
+// one CTA per group of `vecs` 16-byte vectors (a text's tokens / an image's patch rows); a flagged group writes NaN to
+// S[group * s_group + e * s_elem], e < n
+template <typename T>
+__global__ void __launch_bounds__(256) poison_nonfinite_kernel(const uint4* __restrict__ op, long long vecs, float* S,
+                                                               long long s_group, long long s_elem, int n) {
+  const uint4* g = op + static_cast<long long>(blockIdx.x) * vecs;
+  bool bad = false;
+  for (long long i = threadIdx.x; i < vecs; i += blockDim.x) bad |= nonfinite16<T>(__ldg(g + i));
+  if (__syncthreads_or(bad ? 1 : 0)) {
+    float* row = S + static_cast<long long>(blockIdx.x) * s_group;
+    for (int e = threadIdx.x; e < n; e += blockDim.x) row[static_cast<long long>(e) * s_elem] = __int_as_float(0x7FC00000);
+  }
+}
+
+// dtype: CXL_DTYPE_* of the operands; txt [Bt, T*D], img [Bi, p_stride*D] contiguous, 16-byte aligned rows
+int poison_nonfinite(const void* txt, const void* img, int Bt, int Bi, int T, int p_stride, int D, int dtype, float* S,
+                     cudaStream_t stream) {
+  const int es = dtype == CXL_DTYPE_F32 ? 4 : 2;
+  const long long tv = static_cast<long long>(T) * D * es, iv = static_cast<long long>(p_stride) * D * es;
+  if (tv % 16 != 0 || iv % 16 != 0 || ((reinterpret_cast<uintptr_t>(txt) | reinterpret_cast<uintptr_t>(img)) & 15))
+    return CXL_OK;                                          // unaligned operands (odd T*D): no vector scan, no propagation
+#define CXL_POISON(TY)                                                                                                  \
+  poison_nonfinite_kernel<TY><<<Bt, 256, 0, CXL_COUNTED(stream)>>>(static_cast<const uint4*>(txt), tv / 16, S, Bi, 1, Bi); \
+  poison_nonfinite_kernel<TY><<<Bi, 256, 0, CXL_COUNTED(stream)>>>(static_cast<const uint4*>(img), iv / 16, S, 1, Bi, Bt)
+  if (dtype == CXL_DTYPE_BF16) { CXL_POISON(__nv_bfloat16); }
+  else if (dtype == CXL_DTYPE_F16) { CXL_POISON(__half); }
+  else { CXL_POISON(float); }
+#undef CXL_POISON
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
 }  // namespace cxl

@@ -271,6 +271,38 @@ class CudaKernels:
                                           self._dt(dx), _stream()), "cxl_l2norm_bwd")
         return dx
 
+    # ---- global-embedding GEMMs --------------------------------------------------------
+    def gemm_nt(self, a: torch.Tensor, b: torch.Tensor) -> Optional[torch.Tensor]:
+        """C [M,N] f32 = a [M,K] @ b [N,K]^T on the tcgen05 pipeline; a, b contiguous bf16 or fp16 of one dtype.
+        None when the shape is outside the kernel (K % 64 != 0): the caller falls back to its library GEMM."""
+        dev = _require_cuda(a, b)
+        M, K = a.shape
+        N = b.shape[0]
+        if K % 64 != 0 or a.dtype != b.dtype or a.dtype not in (torch.bfloat16, torch.float16):
+            return None
+        a, b = a.contiguous(), b.contiguous()
+        c = torch.empty((M, N), dtype=torch.float32, device=dev)
+        with torch.cuda.device(dev):
+            rc = self.lib.cxl_gemm_nt(_ptr(a), _ptr(b), M, N, K, _TORCH_DT[a.dtype], _ptr(c), N, _stream())
+        if rc == -2:
+            return None
+        check(rc, "cxl_gemm_nt")
+        return c
+
+    def cast_transpose(self, x: torch.Tensor, dtype: torch.dtype, want_plain: bool = True, want_t: bool = True,
+                       scale: Optional[torch.Tensor] = None):
+        """x [R,C] f32 -> (x as `dtype` [R,C] or None, x^T as `dtype` [C,R] or None) in one pass; `scale` (device
+        scalar, optional) is multiplied in before the cast."""
+        dev = _require_cuda(x)
+        x = x.contiguous()
+        R, C = x.shape
+        y = torch.empty((R, C), dtype=dtype, device=dev) if want_plain else None
+        yt = torch.empty((C, R), dtype=dtype, device=dev) if want_t else None
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_cast_transpose(_ptr(x), R, C, _ptr(y), _ptr(yt), _TORCH_DT[dtype], _ptr(scale), _stream()),
+                  "cxl_cast_transpose")
+        return y, yt
+
     # ---- retrieval ---------------------------------------------------------------------------------
     def rank_of_target(self, scores: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best; -1 where the target is

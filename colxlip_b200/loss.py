@@ -257,14 +257,59 @@ class _FwdState:
                  "cl_t", "consumed")
 
 
+_OP_DTYPE = {"bf16": torch.bfloat16, "fp16": torch.float16}
+
+
 def _round_like_gemm_input(x: torch.Tensor, prec: str) -> torch.Tensor:
-    """fp32 copy of the global features as the GEMM sees them (rounded to the operand dtype on the 16-bit paths)."""
+    """The global features as the logits GEMM sees them: a 16-bit copy on the 16-bit paths (what the reference's
+    autocast matmul multiplies, loss.py:252-253 -- and half the bytes in the feature all-gather), fp32 otherwise."""
     x = x.detach()
-    if prec == "bf16":
-        return x.to(torch.bfloat16).float()
-    if prec == "fp16":
-        return x.to(torch.float16).float()
+    if prec in _OP_DTYPE:
+        return x.to(_OP_DTYPE[prec]).contiguous()
     return x.float()
+
+
+def _logits_gemm(k, a: torch.Tensor, b: torch.Tensor) -> torch.Tensor:
+    """a [M,D] @ b [N,D]^T -> fp32 [M,N].  16-bit operands run on the tcgen05 GEMM (cxl_gemm_nt); fp32 operands (the
+    fp32 parity mode) and shapes the kernel does not take (D % 64 != 0) on the library GEMM."""
+    if a.dtype != torch.float32:
+        c = k.gemm_nt(a, b)
+        if c is not None:
+            return c
+        return a.float() @ b.float().T
+    return a @ b.T
+
+
+def _grad_gemms(k, dX: torch.Tensor, rows_op: Optional[torch.Tensor], cols_op: Optional[torch.Tensor]):
+    """(dX @ cols_op, dX^T @ rows_op) for dX [m,n] fp32 = dL/dlogits: the two gradient GEMMs of a logits block
+    X = rows_op [m,D] @ cols_op [n,D]^T (either operand None: that product is skipped).  On the 16-bit paths dX is
+    cast to the operand dtype -- the reference's autocast backward multiplies a 16-bit dlogits too -- in one
+    cast+transpose pass, and both products run on the tcgen05 GEMM."""
+    op = cols_op if cols_op is not None else rows_op
+    if op is None:
+        return None, None
+    if op.dtype == torch.float32:
+        return (dX @ cols_op if cols_op is not None else None), (dX.T @ rows_op if rows_op is not None else None)
+    sc = None
+    if op.dtype == torch.float16:
+        # fp16 copy of dL/dlogits: a power of two puts its largest entry at 2^15 (small entries stay out of the
+        # subnormal range whatever the loss scale is); undone exactly on the [.,D] results
+        sc = _w_scale_from_bound(dX.abs().amax())
+    d16, d16t = k.cast_transpose(dX, op.dtype, want_plain=cols_op is not None, want_t=rows_op is not None,
+                                 scale=None if sc is None else sc[0:1])
+    g_rows = g_cols = None
+    if cols_op is not None:                               # [m,n] x [n,D]: contraction over n
+        g_rows = k.gemm_nt(d16, cols_op.t().contiguous())
+        if g_rows is None:
+            g_rows = d16.float() @ cols_op.float()
+    if rows_op is not None:                               # [n,m] x [m,D]: contraction over m
+        g_cols = k.gemm_nt(d16t, rows_op.t().contiguous())
+        if g_cols is None:
+            g_cols = d16t.float() @ rows_op.float()
+    if sc is not None:
+        g_rows = g_rows * sc[1] if g_rows is not None else None
+        g_cols = g_cols * sc[1] if g_cols is not None else None
+    return g_rows, g_cols
 
 
 class _ColClipLossFn(torch.autograd.Function):
@@ -313,8 +358,8 @@ class _ColClipLossFn(torch.autograd.Function):
                 S[:, r * b:(r + 1) * b] = S_r
                 cnt[:, r * b:(r + 1) * b] = cnt_r
                 del S_r, cnt_r
-        # global CLIP scores (plain library GEMM, fp32 accumulate) -- SURVEY 8 f-1
-        G = g_txt @ g_img.T
+        # global CLIP scores: tcgen05 GEMM on the 16-bit paths (cxl_gemm_nt), fp32 accumulate -- SURVEY 8 f-1
+        G = _logits_gemm(k, g_txt, g_img)
 
         scale = logit_scale.detach().float().reshape(1).to(dev)
         stats = []
@@ -409,9 +454,9 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
     w_scale = _w_scale_from_bound(coef_t * scale / float(b * W)) if prec == "fp16" else None
 
     mult = float(W) if (cfg["gather_with_grad"] and W > 1) else 1.0
-    d_txt = dG @ st.g_img if need[1] else None
-    d_img = _reduce_scatter_rows(dG.T @ st.g_txt, W, group) if need[0] else None
-    del dG
+    d_txt, d_img_all = _grad_gemms(k, dG, st.g_txt if need[0] else None, st.g_img if need[1] else None)
+    d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
+    del dG, d_img_all
 
     # K2: token gradients from the saved argmax, one home rank's shard at a time in rank order (the order fixes the
     # chain of fp32 additions of dTxt: same bits as one call over all images).  K4 (backward half): each dImg
@@ -745,7 +790,7 @@ class _ClipLossFn(torch.autograd.Function):
         all_img = _all_gather_cat(a_img, W, group)
         scale = logit_scale.detach().float().reshape(1).to(dev)
         if not local:
-            G = a_txt @ all_img.T                                     # rows = this rank's texts
+            G = _logits_gemm(k, a_txt, all_img)                       # rows = this rank's texts
             row_lse, col_max, col_sum, diag = k.infonce_stats(G, scale, row0)
             col_lse = col_max + torch.log(col_sum)
             part = row_lse.sum() - 2.0 * diag.sum()
@@ -756,8 +801,8 @@ class _ClipLossFn(torch.autograd.Function):
             ctx.save_for_backward(G, a_txt, all_img, scale, row_lse, col_lse)
         else:
             all_txt = _all_gather_cat(a_txt, W, group)
-            X_i = a_img @ all_txt.T                                   # logits_per_image of this rank's images
-            X_t = a_txt @ all_img.T                                   # logits_per_text of this rank's texts
+            X_i = _logits_gemm(k, a_img, all_txt)                     # logits_per_image of this rank's images
+            X_t = _logits_gemm(k, a_txt, all_img)                     # logits_per_text of this rank's texts
             rl_i, _, _, dg_i = k.infonce_stats(X_i, scale, row0, rows_only=True)
             rl_t, _, _, dg_t = k.infonce_stats(X_t, scale, row0, rows_only=True)
             loss = ((rl_i - dg_i).sum() + (rl_t - dg_t).sum()) / (2.0 * b)
@@ -781,8 +826,8 @@ class _ClipLossFn(torch.autograd.Function):
             dG, dscale = k.infonce_grad(G, scale, g, row0, row_lse, col_lse)
             if W > 1:
                 dist.all_reduce(dscale, group=group)              # every rank holds the full-batch loss
-            d_txt = dG @ all_img if need[1] else None
-            d_img = _reduce_scatter_rows(dG.T @ a_txt, W, group) if need[0] else None
+            d_txt, d_img_all = _grad_gemms(k, dG, a_txt if need[0] else None, all_img if need[1] else None)
+            d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
             mult = float(W) if gwg else 1.0                       # autograd all_gather sums W identical losses
             if mult != 1.0:
                 d_txt = d_txt * mult if d_txt is not None else None
@@ -793,13 +838,14 @@ class _ClipLossFn(torch.autograd.Function):
             dX_i, ds_i = k.infonce_grad(X_i, scale, coef, row0, rl_i, None)
             dX_t, ds_t = k.infonce_grad(X_t, scale, coef, row0, rl_t, None)
             dscale = ds_i + ds_t                                  # this rank's own loss: no reduction
-            d_img = dX_i @ all_txt if need[0] else None
-            d_txt = dX_t @ all_img if need[1] else None
+            # X_i = a_img x all_txt^T: rows grad -> d_img, gathered-operand grad -> all texts; X_t likewise
+            d_img, d_alltxt = _grad_gemms(k, dX_i, a_img if (gwg and need[1]) else None, all_txt if need[0] else None)
+            d_txt, d_allimg = _grad_gemms(k, dX_t, a_txt if (gwg and need[0]) else None, all_img if need[1] else None)
             if gwg:                                               # gathered operands carry grad home (SUM)
                 if need[1]:
-                    d_txt = d_txt + _reduce_scatter_rows(dX_i.T @ a_img, W, group)
+                    d_txt = d_txt + _reduce_scatter_rows(d_alltxt, W, group)
                 if need[0]:
-                    d_img = d_img + _reduce_scatter_rows(dX_t.T @ a_txt, W, group)
+                    d_img = d_img + _reduce_scatter_rows(d_allimg, W, group)
         d_ls = dscale.reshape(ls_shape).to(dt_ls) if need[2] else None
         return (d_img.to(dt_img) if d_img is not None else None,
                 d_txt.to(dt_txt) if d_txt is not None else None, d_ls, None)

@@ -77,6 +77,10 @@ int cxl_pack_operand(const void* src, int src_dtype, long long src_item_stride, 
  *   S      [Bt,Bi] f32 out (final scores).
  *   cnt    [Bt,Bi] f32 out, count of non-zero maxima (no epsilon); may be NULL for MEAN_PLAIN.
  *   argmax [Bi][cxl_argmax_ld(Bt,T)] out or NULL (inference: nothing saved).
+ * Non-finite inputs: torch.max propagates a NaN similarity; the kernels' running max does not, so the operands are
+ * scanned and EVERY score of a text / an image that holds a NaN or Inf element is returned as NaN (the reference can
+ * return +Inf instead of NaN for an Inf operand; either way the loss and its gradients are non-finite, which is what
+ * AMP's GradScaler tests for).
  */
 int cxl_img_row_stride(int P);
 int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype,
@@ -182,6 +186,19 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                      const float* row_lse, const float* col_lse /*[B] global, or NULL*/, const float* cnt /*[B_loc,B] or NULL*/,
                      float* dX, float* dscale_accum, void* stream);
+
+/*
+ * Global-embedding logits and their gradient GEMMs on the tcgen05 pipeline of cxl_maxsim_fwd (plain-GEMM epilogue).
+ * Replaces `image_features @ text_features.T` and its autograd (loss.py:252-253 in ColClipLoss, 132-160 in ClipLoss):
+ *   C[M,N] (f32, row pitch ldc) = A[M,K] * B[N,K]^T,  A / B row-major 16-bit (dtype CXL_DTYPE_BF16 or CXL_DTYPE_F16,
+ *   what the reference's autocast matmul multiplies), fp32 accumulate.  K % 64 == 0, A / B 16-byte aligned;
+ *   other shapes: CXL_ERR_UNSUPPORTED (the caller keeps its library GEMM).
+ * cxl_cast_transpose: X [R,C] f32 -> Y [R,C] and / or Yt [C,R] in the 16-bit dtype (either may be NULL): the operand
+ * copies of dL/dlogits for  d_txt = dG * img  and  d_img = dG^T * txt.  scale_dev: NULL or a device scalar multiplied
+ * in before the cast (a power of two keeps fp16 copies of small gradients out of the subnormal range).
+ */
+int cxl_gemm_nt(const void* A, const void* B, int M, int N, int K, int dtype, float* C, long long ldc, void* stream);
+int cxl_cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtype, const float* scale_dev, void* stream);
 
 /*
  * L2 normalisation of embedding rows fused with the cast to the operand dtype.  Replaces

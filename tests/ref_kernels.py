@@ -122,6 +122,13 @@ class TorchRefKernels:
             dX = dX / (cnt + 1e-8)
         return dX, (t * X).sum().reshape(1)
 
+    def gemm_nt(self, a, b):
+        return a.float() @ b.float().T
+
+    def cast_transpose(self, x, dtype, want_plain=True, want_t=True, scale=None):
+        y = (x if scale is None else x * scale).to(dtype)
+        return (y if want_plain else None), (y.t().contiguous() if want_t else None)
+
     def l2norm_fwd(self, x, out_dtype, save_inv=True):
         xf = x.float()
         inv = 1.0 / xf.norm(dim=-1).clamp_min(1e-12)

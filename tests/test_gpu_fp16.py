@@ -88,7 +88,7 @@ def test_backward_fp16_streaming_kernels(K, shape, loss_scale):
         S0, c0, a0 = K.maxsim_fwd(txt_op, img_op[:h].contiguous(), T, P, "fp16", O.MASKED, True)
         S1, c1, a1 = K.maxsim_fwd(txt_op, img_op[h:].contiguous(), T, P, "fp16", O.MASKED, True)
         torch.testing.assert_close(torch.cat([S0, S1], dim=1), S, rtol=1e-6, atol=1e-7)   # (S sums are atomics: order-free only to fp32 rounding)
-        assert torch.equal(torch.cat([a0, a1]), arg)
+        assert torch.equal(torch.cat([a0, a1])[:, :Bt * T], arg[:, :Bt * T])
         dt2 = torch.empty_like(dtxt)
         p0 = K.maxsim_bwd_shard(txt_op, img_op[:h].contiguous(), a0, w, 0, T, P, "fp16", dtxt=dt2, w_scale=ws)
         p1 = K.maxsim_bwd_shard(txt_op, img_op[h:].contiguous(), a1, w, h, T, P, "fp16", dtxt=dt2, accumulate_txt=True,
@@ -119,7 +119,8 @@ def test_loss_under_fp16_autocast(shape, grad_scale):
         g = x.grad.float().cpu() / grad_scale
         assert torch.isfinite(g).all()
         # token grads on the streaming kernels (D % 128 == 0) carry fp16-rounded pair weights (2^-11 per term)
-        tol = 2e-3 if (n.startswith("token") and D % 128 == 0) else 1e-4
+        # global grads: dL/dlogits enters the gradient GEMMs in fp16 (2^-11 per term), as in the reference's autocast backward
+        tol = 2e-3 if (n.startswith("token") and D % 128 == 0) else (1e-4 if n.startswith("token") else 1e-3)
         assert (g - ref).abs().max().item() <= tol * ref.abs().max().item() + 1e-9, (n, grad_scale)
     assert abs(ls.grad.item() / grad_scale - r_grads["logit_scale"].item()) <= 2e-4 * max(1e-3, abs(r_grads["logit_scale"].item()))
 

@@ -298,7 +298,9 @@ def test_loss_bf16_autocast_vs_reference_golden(path):
     for g, n in zip(grads, NAMES):
         ref = r_grads[n]
         # token grads: the fast backward rounds the pair weights to bf16 (rel 2^-9 per term) when D % 128 == 0
-        tol = 1e-2 if (n.startswith("token") and ref.shape[-1] % 128 == 0) else 5e-5
+        # global features: dL/dlogits enters the gradient GEMMs in bf16 under autocast (the reference's own backward
+        # precision, 2^-9 per term)
+        tol = 1e-2 if (n.startswith("token") and ref.shape[-1] % 128 == 0) else (5e-5 if n.startswith("token") else 4e-3)
         assert (g - ref).abs().max().item() <= tol * ref.abs().max().item() + 1e-9, n
     assert abs(gls - r_grads["logit_scale"].item()) <= 1e-4 * max(1e-3, abs(r_grads["logit_scale"].item()))
 

@@ -81,7 +81,8 @@ def test_loss_and_all_gradients_b1024_vs_device_oracle():
         # bf16-rounded pair weights on both sides, but rounded from fp32 values that differ in their last bits
         # (K3 vs torch softmax): a weight next to a rounding boundary lands one bf16 step (2^-8 of ONE term) apart,
         # and a near-tied argmax may move one term between patches.  Still 5x inside the bf16 tolerance.
-        assert err <= 2e-3 * ref.abs().max().item() + 1e-9, (n, err, ref.abs().max().item())
+        # (global features: dL/dlogits enters the gradient GEMMs in bf16, the reference's own backward precision)
+        assert err <= 4e-3 * ref.abs().max().item() + 1e-9, (n, err, ref.abs().max().item())
     _, f_grads, _ = O.loss_and_grads_blockwise(img, txt, ti, tt, scale, alpha, round_w_bf16=False)
     for x, n in zip(xs, names):                              # north_star bar against the fp32 oracle: rel <= 1e-2
         ref = f_grads[n]
@@ -208,3 +209,33 @@ def test_rank_kernel_rejects_out_of_range_targets(K):
         assert r[2] == -1 and r[3] == -1 and r[5] == -1 and (r[[0, 1, 4]] >= 0).all()
     with pytest.raises(IndexError):
         compute_retrieval(s, [0] * 39 + [6], [[0]] * 6)
+
+
+@pytest.mark.parametrize("prec", ["bf16", "fp16", "fp32"])
+def test_non_finite_operands_poison_their_scores(K, prec):
+    """torch.max propagates NaN (loss.py:35), `x > best` does not.  A NaN / Inf element in a text's tokens
+    or an image's patches must make that text's row / that image's column of S NaN (and leave every other score
+    untouched), so that the loss and its gradients are non-finite for AMP's overflow check."""
+    from colxlip_b200 import ColClipLoss
+    Bt, Bi, T, P, D = 9, 7, 20, 196, 128
+    _, _, ti, tt = _device_inputs(Bi, P, T, D, seed=5, Bt=Bt)
+    mode = O.MASKED
+    clean, _, _ = K.maxsim_fwd(K.prepare(tt, T, prec), K.prepare(ti, K.img_row_stride(P, prec), prec), T, P, prec, mode, False)
+    tt2, ti2 = tt.clone(), ti.clone()
+    tt2[3, 5, 17] = float("nan")
+    tt2[6, 0, 0] = float("inf")
+    ti2[2, 190, 3] = float("-inf")
+    S, _, _ = K.maxsim_fwd(K.prepare(tt2, T, prec), K.prepare(ti2, K.img_row_stride(P, prec), prec), T, P, prec, mode, False)
+    bad = torch.zeros(Bt, Bi, dtype=torch.bool, device="cuda")
+    bad[3], bad[6], bad[:, 2] = True, True, True
+    assert torch.isnan(S[bad]).all()
+    assert torch.equal(S[~bad], clean[~bad])
+    # through the loss: non-finite loss and gradients
+    if prec == "bf16":
+        img, txt, _, _ = _device_inputs(Bt, P, T, D, seed=6)
+        tsq = tt2[:7].clone().requires_grad_()
+        tiq = ti2.clone().requires_grad_()
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            loss = ColClipLoss()(img[:7], txt[:7], tiq, tsq, torch.tensor(14.0, device="cuda"))
+        loss.backward()
+        assert not torch.isfinite(loss) and not torch.isfinite(tsq.grad).all()

@@ -141,7 +141,7 @@ def _single_gpu_path(acc, rank, world, dev):
         for gr, ref, n in zip(grads, g_one, NAMES):
             # token grads: pair weights are rounded to bf16 from fp32 values that differ in their last bits between the
             # two row partitions of K3 -> a few weights land one bf16 step apart (2^-8 of one term)
-            acc.add("self", f"tc gwg={gwg} g_{n}", gr, ref[sl] * mult, 4e-3 if n.startswith("token") else 1e-4)
+            acc.add("self", f"tc gwg={gwg} g_{n}", gr, ref[sl] * mult, 4e-3)
         acc.add("self", f"tc gwg={gwg} g_logit_scale", ls_g, ls_one, 2e-4)
         lo, hi = 16, 20                                                                # lo * T % 16 == 0: streaming slice kernel
         _, part, _ = _run(crit, [t[sl] for t in feats], scale, dev, grad_rows=(lo, hi))

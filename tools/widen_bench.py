@@ -56,8 +56,31 @@ def main():
         loss.backward()
 
     ms = timed(clip_step)
-    out.append({"what": "ClipLoss fwd+bwd B=32768 D=512 (bf16 autocast)", "ms": ms, "pairs_per_s": B / ms * 1e3})
-    del img, txt
+    out.append({"what": "ClipLoss fwd+bwd B=32768 D=512 (bf16 autocast): cxl_gemm_nt x3 + K3", "ms": ms, "pairs_per_s": B / ms * 1e3})
+
+    def eager_clip_step():      # the reference's ClipLoss.forward as eager PyTorch on the same GPU (loss.py:132-181)
+        with torch.autocast("cuda", dtype=torch.bfloat16):
+            lpi = ls * img @ txt.T
+            lpt = ls * txt @ img.T
+            lab = torch.arange(B, device="cuda")
+            loss = (F.cross_entropy(lpi, lab) + F.cross_entropy(lpt, lab)) / 2
+        loss.backward()
+
+    ms_e = timed(eager_clip_step)
+    out.append({"what": "reference ClipLoss algorithm, eager PyTorch bf16 autocast, same GPU", "ms": ms_e, "ours_speedup": ms_e / ms})
+    from colxlip_b200.kernels import default_kernels
+    Kk = default_kernels()
+    a16, b16 = img.detach().to(torch.bfloat16), txt.detach().to(torch.bfloat16)
+    ms_g = timed(lambda: Kk.gemm_nt(a16, b16))
+    out.append({"what": "cxl_gemm_nt [32768,512] x [32768,512]^T -> f32 (resident A)", "ms": ms_g, "TFLOPs": 2.0 * B * B * 512 / ms_g / 1e9})
+    dG = torch.randn(B, B, device="cuda", generator=g)
+    d16, d16t = Kk.cast_transpose(dG, torch.bfloat16)
+    ms_c = timed(lambda: Kk.cast_transpose(dG, torch.bfloat16))
+    out.append({"what": "cxl_cast_transpose [32768,32768] f32 -> bf16 + bf16^T", "ms": ms_c, "GBps": B * B * 8 / ms_c / 1e6})
+    bt = b16.t().contiguous()
+    ms_g2 = timed(lambda: Kk.gemm_nt(d16, bt))
+    out.append({"what": "cxl_gemm_nt [32768,32768] x [512,32768]^T -> f32 (streamed A, K = 32768)", "ms": ms_g2, "TFLOPs": 2.0 * B * B * 512 / ms_g2 / 1e9})
+    del img, txt, dG, d16, d16t, a16, b16, bt
     # f-4: accumulation step at B=4096 (4 sub-batches of 1024), ViT-B/16 geometry
     B, P, T, D, acc = 4096, 196, 77, 512, 4
     feats = [F.normalize(torch.randn(B, D, device="cuda", generator=g), dim=-1).to(torch.bfloat16),
