@@ -434,6 +434,27 @@ def run_gpu(args):
         except Exception as e:                                  # never lose the measured line to the checker
             dist_parity = {"ok": False, "world": world, "error": f"{type(e).__name__}: {e}"[:300]}
 
+    # ---- per-phase split of one more (untimed) step: CUDA events at the phase boundaries of this rank's stream ----
+    phases = None
+    if not args.no_phases:
+        from colxlip_b200 import loss as _L
+        barrier()
+        _L.phase_recording(True)
+        step(feats)
+        torch.cuda.synchronize()
+        pt = _L.phase_times_ms()
+        _L.phase_recording(False)
+        pv = torch.tensor([ms_ for _, ms_ in pt], device=dev, dtype=torch.float64)
+        if world > 1:
+            pmax = pv.clone()
+            dist.all_reduce(pmax, op=dist.ReduceOp.MAX)
+            dist.all_reduce(pv, op=dist.ReduceOp.SUM)
+            pv /= world
+        else:
+            pmax = pv
+        phases = [{"phase": n, "ms_mean_over_ranks": round(a, 2), "ms_max_over_ranks": round(b_, 2)}
+                  for (n, _), a, b_ in zip(pt, pv.tolist(), pmax.tolist())]
+
     # ---- free the step's buffers, then the extra legs (outside every timed region) ----
     for x in feats + dev_in:
         x.grad = None
@@ -472,6 +493,8 @@ def run_gpu(args):
         }
         if dist_parity is not None:
             line["dist_parity"] = dist_parity
+        if phases is not None:
+            line["phases"] = phases
         if gpu_ref is not None:
             line["gpu_reference"] = gpu_ref
         if cfg5 is not None:
@@ -497,6 +520,7 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-dist-parity", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true")
+    ap.add_argument("--no-phases", action="store_true", help="skip the per-phase CUDA-event split (one extra untimed step)")
     ap.add_argument("--no-cfg5", action="store_true", help="skip the config-5 field of the 8-GPU line")
     args = ap.parse_args()
     # stdout carries exactly ONE line, the JSON result: anything libraries print to fd 1 meanwhile (NCCL's version /

@@ -2,8 +2,8 @@
 lezhang7/colxlip's `colxlip.loss` API.  CUDA only; there is no CPU fallback."""
 from .loss import (ClipLoss, ColClipAccumulation, ColClipLoss, compute_colbert_similarity, compute_colbert_similarity_mean, gather_features,
                    get_precision, set_precision)
-from .model import ColXLIPScoringMixin, normalize_tokens, patch_colxlip
+from .model import ColXLIPScoringMixin, TokenHead, encode_tokens, eot_valid_len, normalize_tokens, patch_colxlip
 from .retrieval import compute_retrieval, maxsim_score_matrix, retrieval_on_split
 
 __all__ = ["ClipLoss", "ColClipAccumulation", "ColClipLoss", "compute_colbert_similarity", "compute_colbert_similarity_mean", "gather_features",
-           "ColXLIPScoringMixin", "patch_colxlip", "normalize_tokens", "compute_retrieval", "maxsim_score_matrix", "retrieval_on_split", "set_precision", "get_precision"]
+           "ColXLIPScoringMixin", "patch_colxlip", "normalize_tokens", "TokenHead", "encode_tokens", "eot_valid_len", "compute_retrieval", "maxsim_score_matrix", "retrieval_on_split", "set_precision", "get_precision"]

@@ -60,6 +60,10 @@ SYMBOLS = {
     "cxl_l2norm_bwd": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_longlong, c_int, c_void_p, c_int, c_void_p]),
     "cxl_gemm_nt": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_longlong, c_void_p]),
     "cxl_cast_transpose": (c_int, [c_void_p, c_int, c_int, c_void_p, c_void_p, c_int, c_void_p, c_void_p]),
+    "cxl_head_ln_in": (c_int, [c_void_p, c_int, c_longlong, c_int, c_void_p, c_void_p, c_float, c_void_p, c_int, c_void_p,
+                               c_int, c_void_p]),
+    "cxl_head_out": (c_int, [c_void_p, c_longlong, c_int, c_void_p, c_void_p, c_void_p, c_float, c_int, c_void_p, c_int,
+                             c_void_p]),
     "cxl_rank_of_target": (c_int, [c_void_p, c_longlong, c_longlong, c_int, c_int, c_void_p, c_void_p, c_void_p]),
     "cxl_maxsim_fwd_tc_ex": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                      c_void_p, c_void_p, c_void_p, c_int, c_int, c_void_p]),

@@ -11,7 +11,7 @@ PKG_DIR = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG_DIR, "csrc")
 BUILD = os.path.join(PKG_DIR, "csrc", "build")
 LIB_PATH = os.path.join(PKG_DIR, "libcolxlip_b200.so")
-SOURCES = ["api.cu", "maxsim_fwd_tc.cu", "maxsim_fwd_f32.cu", "maxsim_bwd.cu", "maxsim_bwd_v2.cu", "maxsim_bwd_dimg4.cu", "infonce.cu", "misc.cu", "l2norm.cu"]
+SOURCES = ["api.cu", "maxsim_fwd_tc.cu", "maxsim_fwd_f32.cu", "maxsim_bwd.cu", "maxsim_bwd_v2.cu", "maxsim_bwd_dimg4.cu", "infonce.cu", "misc.cu", "l2norm.cu", "token_head.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC", "--expt-relaxed-constexpr"]
 

@@ -53,6 +53,10 @@ int pack_operand(const void* src, int src_dtype, long long item_stride, long lon
                  int n_pad, int D, void* dst, int dst_dtype, cudaStream_t stream);
 int gemm_nt_tc(const void* A, const void* B, int M, int N, int K, float* C, long long ldc, int f16, cudaStream_t stream);
 int cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtype, const float* scale, cudaStream_t stream);
+int head_ln_in(const void* x, int x_dtype, long long rows, int width, const float* gamma, const float* beta, float eps,
+               const int* valid_len, int T, void* y, int y_dtype, cudaStream_t stream);
+int head_out(const float* h, long long rows, int D, const float* bias, const float* gamma, const float* beta, float eps,
+             int l2_normalize, void* y, int y_dtype, cudaStream_t stream);
 int poison_nonfinite(const void* txt, const void* img, int Bt, int Bi, int T, int p_stride, int D, int dtype, float* S,
                      cudaStream_t stream);
 int rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,
@@ -291,6 +295,22 @@ int cxl_cast_transpose(const float* X, int R, int C, void* Y, void* Yt, int dtyp
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   return cast_transpose(X, R, C, Y, Yt, dtype, scale_dev, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_head_ln_in(const void* x, int x_dtype, long long rows, int width, const float* gamma, const float* beta, float eps,
+                   const int* valid_len, int T, void* y, int y_dtype, void* stream) {
+  if (!x || !y || !gamma || !beta) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return head_ln_in(x, x_dtype, rows, width, gamma, beta, eps, valid_len, T, y, y_dtype, static_cast<cudaStream_t>(stream));
+}
+
+int cxl_head_out(const float* h, long long rows, int D, const float* bias, const float* gamma, const float* beta,
+                 float eps, int l2_normalize, void* y, int y_dtype, void* stream) {
+  if (!h || !y || !bias || !gamma || !beta) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return head_out(h, rows, D, bias, gamma, beta, eps, l2_normalize, y, y_dtype, static_cast<cudaStream_t>(stream));
 }
 
 int cxl_rank_of_target(const float* scores, long long row_stride, long long col_stride, int rows, int cols,

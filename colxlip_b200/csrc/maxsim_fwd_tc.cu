@@ -757,6 +757,18 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
         if (static_cast<double>(u) >= 0.97 * static_cast<double>(waves * clusters)) break;
       }
       q.tiles_per_unit = (q.total_n_tiles + chunks2 - 1) / chunks2;
+      // Image blocks: units are ordered chunk-major, so all clusters work on the SAME block of images at a time.  A block
+      // that fits L2 (CXL_K1_IMG_BLOCK images, default 384 = 77 MB of bf16 patches at P 196, D 512) is pulled from DRAM
+      // once and re-read from L2 by every wave of row-pair units; whole sweeps per unit re-stream the 6.6 GB operand
+      // from DRAM for every wave (measured 6.77 TB of DRAM reads per cfg-2 launch).  Costs one extra text-tile load
+      // (128 KB) per unit.
+      {
+        static const int blk_env = getenv("CXL_K1_IMG_BLOCK") ? atoi(getenv("CXL_K1_IMG_BLOCK")) : 384;
+        if (blk_env > 0 && q.tiles_per_unit > blk_env && q.num_m_tiles >= 4 * clusters) {
+          const int nblk = (q.total_n_tiles + blk_env - 1) / blk_env;
+          q.tiles_per_unit = (q.total_n_tiles + nblk - 1) / nblk;
+        }
+      }
       // packed tiles (opt-in, CXL_K1_PACK=1): groups of g images with g*P % 16 == 0 share g tiles without pad columns
       int extra_smem = 0;
       static const int pack_env = getenv("CXL_K1_PACK") ? atoi(getenv("CXL_K1_PACK")) : 0;

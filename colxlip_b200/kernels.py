@@ -303,6 +303,39 @@ class CudaKernels:
                   "cxl_cast_transpose")
         return y, yt
 
+    # ---- token heads (SURVEY 8 f-3) -----------------------------------------------------------------------
+    def token_head(self, x: torch.Tensor, ln1_w, ln1_b, lin_w, lin_b, ln2_w, ln2_b, out_dtype: torch.dtype,
+                   op_dtype: torch.dtype = torch.bfloat16, valid_len: Optional[torch.Tensor] = None,
+                   normalize: bool = True, eps1: float = 1e-5, eps2: float = 1e-5) -> Optional[torch.Tensor]:
+        """[N, T, width] -> [N, T, D]: LayerNorm -> Linear -> GELU -> LayerNorm (-> L2 normalise) in three launches
+        (cxl_head_ln_in, cxl_gemm_nt, cxl_head_out).  valid_len [N] int32: tokens at positions >= valid_len[n] enter the
+        head as zeros (EOT masking).  None when the widths are outside the kernels (caller keeps its torch modules)."""
+        dev = _require_cuda(x, lin_w)
+        N, T, width = x.shape
+        D = lin_w.shape[0]
+        if width % 256 or width > 1024 or D % 256 or D > 1024 or x.dtype not in _TORCH_DT:
+            return None
+        if x.dtype != torch.float32 and x.dtype != op_dtype:
+            x = x.float()
+        x = x.contiguous()
+        rows = N * T
+        f32 = lambda t: t.detach().float().contiguous()                                                   # noqa: E731
+        g1, b1, g2, b2, lb = f32(ln1_w), f32(ln1_b), f32(ln2_w), f32(ln2_b), f32(lin_b)
+        w16 = lin_w.detach().to(op_dtype).contiguous()
+        a16 = torch.empty((rows, width), dtype=op_dtype, device=dev)
+        vl = None if valid_len is None else valid_len.to(device=dev, dtype=torch.int32).contiguous()
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_head_ln_in(_ptr(x), _TORCH_DT[x.dtype], rows, width, _ptr(g1), _ptr(b1), eps1, _ptr(vl), T,
+                                          _ptr(a16), _TORCH_DT[op_dtype], _stream()), "cxl_head_ln_in")
+        h = self.gemm_nt(a16, w16)
+        if h is None:
+            return None
+        y = torch.empty((N, T, D), dtype=out_dtype, device=dev)
+        with torch.cuda.device(dev):
+            check(self.lib.cxl_head_out(_ptr(h), rows, D, _ptr(lb), _ptr(g2), _ptr(b2), eps2, 1 if normalize else 0,
+                                        _ptr(y), _TORCH_DT[out_dtype], _stream()), "cxl_head_out")
+        return y
+
     # ---- retrieval ---------------------------------------------------------------------------------
     def rank_of_target(self, scores: torch.Tensor, target: torch.Tensor) -> torch.Tensor:
         """scores [R,C] fp32 (any strides), target [R] int32 -> rank [R] int32 (0 = best; -1 where the target is

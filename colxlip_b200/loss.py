@@ -212,6 +212,28 @@ def _dimg_chunk_images(b: int, P: int, D: int) -> int:
 
 _COMM_STREAMS = {}
 
+# ---- per-phase CUDA-event split of a step (bench.py reports it as "phases"; off unless a recorder is installed) ----
+_PHASE_REC = None
+
+
+def phase_recording(on: bool = True):
+    """Install / remove the phase recorder; `phase_times_ms()` after a synchronize() returns [(name, ms since the
+    previous mark)] of the marks recorded on the current stream since the recorder was installed."""
+    global _PHASE_REC
+    _PHASE_REC = [] if on else None
+
+
+def _mark(name: str, dev) -> None:
+    if _PHASE_REC is not None and dev.type == "cuda":
+        ev = torch.cuda.Event(enable_timing=True)
+        ev.record(torch.cuda.current_stream(dev))
+        _PHASE_REC.append((name, ev))
+
+
+def phase_times_ms():
+    rec = _PHASE_REC or []
+    return [(rec[i][0], rec[i - 1][1].elapsed_time(rec[i][1])) for i in range(1, len(rec))]
+
 
 def _comm_stream(dev: torch.device):
     """Side stream for the shard broadcasts / dImg reductions, so they overlap K1 / K2 on the current stream."""
@@ -337,6 +359,7 @@ class _ColClipLossFn(torch.autograd.Function):
 
         # global features first (small collectives), then the token operand: one broadcast per home rank on a side
         # stream (K4, forward half) -- K1 runs on the local shard while the remote ones arrive
+        _mark("step_start", dev)
         g_txt = _round_like_gemm_input(text_features, prec)
         g_img = _all_gather_cat(_round_like_gemm_input(image_features, prec), W, group)
         txt_op = k.prepare(token_text_features, T, prec)
@@ -358,6 +381,7 @@ class _ColClipLossFn(torch.autograd.Function):
                 S[:, r * b:(r + 1) * b] = S_r
                 cnt[:, r * b:(r + 1) * b] = cnt_r
                 del S_r, cnt_r
+        _mark("fwd: gather issue + K1 (all shards)", dev)
         # global CLIP scores: tcgen05 GEMM on the 16-bit paths (cxl_gemm_nt), fp32 accumulate -- SURVEY 8 f-1
         G = _logits_gemm(k, g_txt, g_img)
 
@@ -374,6 +398,7 @@ class _ColClipLossFn(torch.autograd.Function):
             stats.append((row_lse, col_lse, loss))
         loss_g, loss_t = stats[0][2], stats[1][2]
         total = alpha * loss_g + (1.0 - alpha) * loss_t
+        _mark("fwd: global GEMM + K3 statistics + column-LSE exchange", dev)
 
         if need_bwd:
             st = _FwdState()
@@ -436,6 +461,7 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
     txt_op, cnt, S, G, scale = st.txt_op, st.cnt, st.S, st.G, st.scale
     D = txt_op.shape[2]
     dev = txt_op.device
+    _mark("(between forward and backward)", dev)
     g = g.float()
     coef_g = (g[0] + alpha * g[2]).reshape(1).contiguous()
     coef_t = (g[1] + (1.0 - alpha) * g[2]).reshape(1).contiguous()
@@ -458,6 +484,7 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
     d_img = _reduce_scatter_rows(d_img_all, W, group) if need[0] else None
     del dG, d_img_all
 
+    _mark("bwd: K3 gradient + global gradient GEMMs + their reduce-scatter", dev)
     # K2: token gradients from the saved argmax, one home rank's shard at a time in rank order (the order fixes the
     # chain of fp32 additions of dTxt: same bits as one call over all images).  K4 (backward half): each dImg
     # partial is SUM-reduced to its home rank while K2 works on the next one; gather_with_grad=True reproduces the
@@ -508,8 +535,10 @@ def _colclip_backward(st, cfg, meta, g, need, consume=False):
         if consume and W > 1:
             st.shards[r] = None                     # this rank is done with home rank r's images: 1/W of the gathered
             st.args[r] = None                       # operand and of the argmax go back to the allocator now
+    _mark("bwd: K2 over all shards (dImg reductions overlapped on the side stream)", dev)
     if inflight:
         torch.cuda.current_stream(dev).wait_stream(_comm_stream(dev))
+    _mark("bwd: wait for the last dImg reduction", dev)
     dimg_tok = out_ref[0] if need[2] else None
     if consume:
         st.shards = st.args = None

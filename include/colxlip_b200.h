@@ -215,6 +215,22 @@ int cxl_l2norm_bwd(const void* y, int y_dtype, const void* g, int g_dtype, const
                    int D, void* dx, int dx_dtype, void* stream);
 
 /*
+ * Token heads of ColXLIP (model.py:518-530: LayerNorm -> Linear -> GELU -> LayerNorm), the EOT masking of the text
+ * tokens in front of them (model.py:580-593) and the L2 normalise + operand cast behind them (model.py:551-554,
+ * 605-607; loss.py:34), as three launches: cxl_head_ln_in -> cxl_gemm_nt -> cxl_head_out.
+ *   cxl_head_ln_in: y[r,:] = LayerNorm(x[r,:]) * gamma + beta over `width` channels, written in the 16-bit GEMM dtype;
+ *       valid_len (device int [rows / T], may be NULL): rows with (r % T) >= valid_len[r / T] are computed from a ZERO
+ *       input, as the reference zeroes the tokens at and after the EOT position before the head (so y = beta there).
+ *   cxl_head_out:   y[r,:] = [L2 normalise] LayerNorm(GELU(h[r,:] + bias)) * gamma + beta, h [rows, D] fp32 = the GEMM
+ *       output; exact (erf) GELU; y in bf16 / fp16 (K1's operand layout for P >= 128) or f32.
+ * width and D: multiples of 256, at most 1024; gamma / beta / bias fp32, 16-byte aligned.
+ */
+int cxl_head_ln_in(const void* x, int x_dtype, long long rows, int width, const float* gamma, const float* beta, float eps,
+                   const int* valid_len, int T, void* y, int y_dtype, void* stream);
+int cxl_head_out(const float* h, long long rows, int D, const float* bias, const float* gamma, const float* beta,
+                 float eps, int l2_normalize, void* y, int y_dtype, void* stream);
+
+/*
  * Retrieval ranking: rank of the ground-truth column in every row of a score matrix
  * (number of entries strictly greater, ties broken by lower index first, as a stable
  * descending argsort does).  Replaces the per-row argsort loop of train.py:467-469.

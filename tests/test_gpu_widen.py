@@ -350,3 +350,50 @@ def test_cliploss_b4096_on_the_tensor_core_gemms():
         assert (x.grad - y.grad).abs().max() <= 4e-3 * y.grad.abs().max()
         assert ((x.grad - y.grad).norm() / y.grad.norm()).item() <= 4e-3
     assert abs(ls.grad.item() - ls2.grad.item()) <= 1e-4 * abs(ls2.grad.item())
+
+
+# ---- f-3: token heads + EOT masking + L2 normalise as three launches -----------------------------------------------
+@pytest.mark.parametrize("N,T,width,D,dtype", [(37, 77, 512, 512, torch.bfloat16), (9, 196, 768, 512, torch.bfloat16),
+                                               (5, 577, 1024, 768, torch.bfloat16), (16, 77, 768, 768, torch.float16)])
+def test_fused_token_head(N, T, width, D, dtype):
+    import torch.nn as nn
+    from colxlip_b200 import TokenHead, encode_tokens
+    torch.manual_seed(N)
+    head = TokenHead(width, D).cuda()
+    with torch.no_grad():
+        for p_ in head.parameters():
+            p_.add_(0.1 * torch.randn_like(p_))
+    ref = nn.Sequential(nn.LayerNorm(width), nn.Linear(width, D), nn.GELU(), nn.LayerNorm(D)).cuda()
+    ref.load_state_dict(head.state_dict())
+    x = torch.randn(N, T, width, device="cuda") * 2 + 0.3
+    vl = torch.randint(1, T + 1, (N,), device="cuda", dtype=torch.int32) if T == 77 else None
+    xm = x if vl is None else x * (torch.arange(T, device="cuda")[None, :] < vl[:, None])[..., None]
+    with torch.autocast("cuda", dtype=dtype):
+        y = encode_tokens(x, head, valid_len=vl, normalize=True)
+        y_ac = torch.nn.functional.normalize(ref(xm), dim=-1)        # the reference's op sequence under autocast
+    assert y.dtype == dtype and y.shape == (N, T, D)
+    y32 = torch.nn.functional.normalize(ref(xm), dim=-1)             # fp32 ground truth
+    # operands of the Linear are rounded to 16 bits (as under autocast); everything else is fp32 here, so the fused
+    # result is at least as close to fp32 as the reference's own autocast pipeline
+    e_fused = (y.float() - y32).abs().max().item()
+    e_ac = (y_ac.float() - y32).abs().max().item()
+    assert e_fused <= 1e-2 and e_fused <= 1.5 * e_ac + 2e-3, (e_fused, e_ac)
+    torch.testing.assert_close(y.float().norm(dim=-1), torch.ones(N, T, device="cuda"), rtol=0, atol=1e-2)
+    # goes straight into the scorer without a pack pass
+    if vl is not None:
+        assert torch.equal(y[0, int(vl[0]):].float().std(dim=0), torch.zeros(D, device="cuda")) or int(vl[0]) >= T - 1
+    # backward = autograd of the reference's ops on the saved input (recompute)
+    xr = x.clone().requires_grad_()
+    with torch.autocast("cuda", dtype=dtype):
+        yf = encode_tokens(xr, head, valid_len=vl, normalize=True)
+    g = torch.randn_like(yf)
+    yf.backward(g)
+    xr2 = x.clone().requires_grad_()
+    ref.zero_grad()
+    with torch.autocast("cuda", dtype=dtype):
+        xm2 = xr2 if vl is None else xr2 * (torch.arange(T, device="cuda")[None, :] < vl[:, None])[..., None]
+        y2 = torch.nn.functional.normalize(ref(xm2), dim=-1)
+    y2.backward(g.to(y2.dtype))
+    assert (xr.grad - xr2.grad).abs().max() <= 2e-2 * xr2.grad.abs().max() + 1e-6
+    for (n1, p1), (n2, p2) in zip(head.named_parameters(), ref.named_parameters()):
+        assert (p1.grad - p2.grad).abs().max() <= 2e-2 * p2.grad.abs().max() + 1e-6, n1

@@ -253,3 +253,29 @@ def test_accumulation_shared_forward_equals_reference_loop():
         state.slice_loss(0, sub, *bad, ls, verify=True)
     with pytest.raises(ValueError):
         state.slice_loss(0, sub + 1, *[t[0:sub] for t in feats], ls)
+
+
+def test_token_head_is_state_dict_compatible_and_masks_like_the_reference():
+    """TokenHead = the reference's nn.Sequential(LayerNorm, Linear, GELU, LayerNorm) (model.py:518-530): same keys, same
+    CPU results; encode_tokens zeroes the tokens at and after the EOT position BEFORE the head (model.py:580-593)."""
+    import torch.nn as nn
+    from colxlip_b200 import TokenHead, encode_tokens, eot_valid_len
+    torch.manual_seed(0)
+    ref = nn.Sequential(nn.LayerNorm(64), nn.Linear(64, 32), nn.GELU(), nn.LayerNorm(32))
+    head = TokenHead(64, 32)
+    assert list(head.state_dict().keys()) == list(ref.state_dict().keys())
+    head.load_state_dict(ref.state_dict())
+    x = torch.randn(3, 7, 64)
+    torch.testing.assert_close(head(x), ref(x))
+    text = torch.tensor([[5, 9, 49407, 0, 0, 0, 0], [3, 49407, 0, 0, 0, 0, 0], [1, 2, 3, 4, 5, 6, 49407]])
+    vl = eot_valid_len(text)
+    assert vl.tolist() == [2, 1, 6]
+    # the reference's masking (model.py:583-593)
+    seq = torch.arange(7)[None, :].expand(3, -1)
+    mask = seq < text.argmax(dim=-1)[:, None]
+    masked = torch.zeros_like(x)
+    masked[mask] = x[mask]
+    want = torch.nn.functional.normalize(ref(masked), dim=-1)
+    got = encode_tokens(x, head, valid_len=vl, normalize=True)
+    torch.testing.assert_close(got, want)
+    assert torch.allclose(got[0, 2], got[1, 5])                  # masked positions all carry the head's image of zero
