@@ -758,12 +758,15 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       }
       q.tiles_per_unit = (q.total_n_tiles + chunks2 - 1) / chunks2;
       // Image blocks: units are ordered chunk-major, so all clusters work on the SAME block of images at a time.  A block
-      // that fits L2 (CXL_K1_IMG_BLOCK images, default 384 = 77 MB of bf16 patches at P 196, D 512) is pulled from DRAM
-      // once and re-read from L2 by every wave of row-pair units; whole sweeps per unit re-stream the 6.6 GB operand
-      // from DRAM for every wave (measured 6.77 TB of DRAM reads per cfg-2 launch).  Costs one extra text-tile load
-      // (128 KB) per unit.
+      // that fits L2 (CXL_K1_IMG_BLOCK images, default 192 = 38 MB of bf16 patches at P 196, D 512; the two dies each
+      // cache their own copy, so 384 images = 77 MB already thrash the 126 MB L2) is pulled from DRAM once and re-read
+      // from L2 by every wave of row-pair units; whole sweeps per unit re-stream the 6.6 GB operand from DRAM for every
+      // wave.  Costs one extra text-tile load (128 KB) per unit.  K1 is power-capped, so DRAM energy is clock:
+      // one B200, [16384 x 32768] launches interleaved: block 0 5871 / 5949 ms, 96 5810, 192 5801 / 5807, 384 6161 ms;
+      // [4096 x 32768]: 1473 -> 1450 ms, DRAM reads 534 -> 150 GB; one [4096 x 4096] shard of the 8-GPU pipeline
+      // 180.8 -> 176.1 ms (profiles/r4j_k1_img_block_ab_1gpu.txt, r4j_k1_img_block_ncu.txt).
       {
-        static const int blk_env = getenv("CXL_K1_IMG_BLOCK") ? atoi(getenv("CXL_K1_IMG_BLOCK")) : 384;
+        static const int blk_env = getenv("CXL_K1_IMG_BLOCK") ? atoi(getenv("CXL_K1_IMG_BLOCK")) : 192;
         if (blk_env > 0 && q.tiles_per_unit > blk_env && q.num_m_tiles >= 4 * clusters) {
           const int nblk = (q.total_n_tiles + blk_env - 1) / blk_env;
           q.tiles_per_unit = (q.total_n_tiles + nblk - 1) / nblk;
