@@ -54,6 +54,8 @@ SYMBOLS = {
     "cxl_infonce_workspace_bytes": (c_size_t, [c_int, c_int]),
     "cxl_infonce_stats": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
                                   c_void_p, c_size_t, c_void_p]),
+    "cxl_infonce_stats_static": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p, c_void_p,
+                                         c_void_p]),
     "cxl_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_void_p]),
     "cxl_l2norm_fwd": (c_int, [c_void_p, c_int, c_longlong, c_int, c_void_p, c_int, c_void_p, c_void_p]),

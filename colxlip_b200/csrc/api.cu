@@ -44,6 +44,8 @@ int pair_weights(const float* dS, const float* cnt, const float* gscale, int mea
 size_t infonce_workspace_bytes(int B_loc, int B);
 int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse, float* col_max,
                   float* col_sum, float* diag, void* ws, size_t ws_bytes, cudaStream_t stream);
+int infonce_stats_static(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse,
+                         float* col_max, float* col_sum, float* diag, cudaStream_t stream);
 int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                  const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
                  cudaStream_t stream);
@@ -90,6 +92,9 @@ const char* cxl_strerror(int code) {
     case CXL_ERR_CUDA: return "CUDA call failed (see cxl_last_cuda_error)";
     case CXL_ERR_NO_DEVICE: return "no sm_100 (Blackwell B200) device; there is no CPU fallback";
     case CXL_ERR_WORKSPACE: return "workspace too small";
+    case CXL_ERR_STATIC_SCRATCH:
+      return "problem exceeds the built-in static scratch of this *_static entry point (see its size limit in "
+             "colxlip_b200.h); use the workspace-taking entry point";
     default: return "unknown error";
   }
 }
@@ -253,6 +258,15 @@ int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, 
   if (rc != CXL_OK) return rc;
   return infonce_stats(X, scale_dev, B_loc, B, row0, row_lse, col_max, col_sum, diag, ws, ws_bytes,
                        static_cast<cudaStream_t>(stream));
+}
+
+int cxl_infonce_stats_static(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse,
+                             float* col_max, float* col_sum, float* diag, void* stream) {
+  if (!X || !scale_dev || !row_lse || !col_max || !col_sum || !diag) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return infonce_stats_static(X, scale_dev, B_loc, B, row0, row_lse, col_max, col_sum, diag,
+                              static_cast<cudaStream_t>(stream));
 }
 
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,

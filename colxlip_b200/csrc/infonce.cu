@@ -4,6 +4,8 @@
 // Replaces `logit_scale * S`, `.T` and the four F.cross_entropy calls of the reference
 // (loss.py:252-263, 285-293) and their autograd (log_softmax / nll_loss backward).
 // Rows are this rank's texts (global row index row0 + m), columns are all B images.
+#include <mutex>
+
 #include "common.cuh"
 
 namespace cxl {
@@ -233,5 +235,57 @@ int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, 
   CXL_CUDA_CHECK(cudaGetLastError());
   return CXL_OK;
 }
+
+// ---- allocation-free statistics pass: column partials in a file-scope device array ----------------------------
+// (no counterpart in the reference; added for callers that may not call
+// cudaMalloc: CUDA-graph capture, tight serving loops.)  Every device that loads the library holds
+// kInfonceStaticScratchBytes until exit.  All calls on one device share the array: calls that overlap on the GPU
+// (different streams) race.  Nothing in it has to start at zero: the partial kernel writes every (row block, column)
+// cell the combine kernel reads, so stale contents of an earlier call are never consumed.
+static constexpr size_t kInfonceStaticScratchBytes = size_t(CXL_INFONCE_STATIC_SCRATCH_BYTES);
+static __device__ __align__(256) unsigned char g_infonce_static_scratch[kInfonceStaticScratchBytes];
+
+static constexpr int kMaxStaticDevices = 64;
+static std::mutex g_static_mu;
+static void* g_static_ptr[kMaxStaticDevices];        // device address of the array, per device ordinal (0 = not yet asked)
+
+// The array's name is a host-side stand-in here, not a device address: ask the runtime once per device, with that
+// device current (the caller's current device is where its stream and buffers live).
+static int infonce_static_scratch(void** out) {
+  int dev = -1;
+  CXL_CUDA_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kMaxStaticDevices) return CXL_ERR_UNSUPPORTED;
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (g_static_ptr[dev] == nullptr) {
+    void* p = nullptr;
+    CXL_CUDA_CHECK(cudaGetSymbolAddress(&p, g_infonce_static_scratch));
+    if (p == nullptr) return CXL_ERR_CUDA;
+    g_static_ptr[dev] = p;
+  }
+  *out = g_static_ptr[dev];
+  return CXL_OK;
+}
+
+int infonce_stats_static(const float* X, const float* scale_dev, int B_loc, int B, int row0, float* row_lse,
+                         float* col_max, float* col_sum, float* diag, cudaStream_t stream) {
+  if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
+  if (col_max == nullptr || col_sum == nullptr) return CXL_ERR_INVALID_ARG;   // rows-only needs no scratch: cxl_infonce_stats
+  if (infonce_workspace_bytes(B_loc, B) > kInfonceStaticScratchBytes) return CXL_ERR_STATIC_SCRATCH;
+  void* scratch = nullptr;
+  const int rc = infonce_static_scratch(&scratch);
+  if (rc != CXL_OK) return rc;
+  const int nblk = (B_loc + kColRowsPerBlock - 1) / kColRowsPerBlock;
+  float* pmax = reinterpret_cast<float*>(scratch);
+  float* psum = pmax + static_cast<size_t>(nblk) * B;
+  infonce_row_kernel<<<B_loc, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B, row0, row_lse, diag);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  dim3 g((B + 511) / 512, nblk);
+  infonce_col_partial_kernel<<<g, 128, 0, CXL_COUNTED(stream)>>>(X, scale_dev, B_loc, B, pmax, psum);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  infonce_col_combine_kernel<<<(B + 255) / 256, 256, 0, CXL_COUNTED(stream)>>>(pmax, psum, nblk, B, col_max, col_sum);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
 
 }  // namespace cxl

@@ -31,6 +31,7 @@ extern "C" {
 #define CXL_ERR_CUDA (-3)          /* a CUDA runtime/driver call failed (see cxl_last_cuda_error) */
 #define CXL_ERR_NO_DEVICE (-4)     /* no sm_100 device: there is NO CPU fallback             */
 #define CXL_ERR_WORKSPACE (-5)     /* workspace too small                                   */
+#define CXL_ERR_STATIC_SCRATCH (-6) /* problem needs more than the built-in scratch of a *_static entry point */
 
 #define CXL_DTYPE_F32 0
 #define CXL_DTYPE_BF16 1
@@ -174,6 +175,22 @@ size_t cxl_infonce_workspace_bytes(int B_loc, int B);
 int cxl_infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int row0,
                       float* row_lse /*[B_loc]*/, float* col_max /*[B]*/, float* col_sum /*[B]*/,
                       float* diag /*[B_loc] scale*X[m,row0+m]*/, void* ws, size_t ws_bytes, void* stream);
+/*
+ * Allocation-free variant of cxl_infonce_stats (both directions): the column partials live in a file-scope
+ * __device__ array inside the library instead of a caller workspace, so the call needs no cudaMalloc on either side
+ * (CUDA-graph capture, tight serving loops, harnesses that forbid allocation).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels, same results as cxl_infonce_stats.
+ *   - limit: cxl_infonce_workspace_bytes(B_loc, B) <= CXL_INFONCE_STATIC_SCRATCH_BYTES (16 MiB: e.g. B_loc = B <= 16384,
+ *     or one rank of 8 at B = 65536 with B_loc = 4096); larger problems return CXL_ERR_STATIC_SCRATCH and launch nothing;
+ *   - col_max and col_sum are required (the rows-only form of cxl_infonce_stats needs no scratch at all);
+ *   - every GPU that loads the library holds the 16 MiB until the process exits;
+ *   - all calls on one device share the array: calls that may overlap on the GPU (different streams) race -- order
+ *     them on one stream or with events.  Nothing in the array has to be cleared between calls.
+ */
+#define CXL_INFONCE_STATIC_SCRATCH_BYTES (16u << 20)
+int cxl_infonce_stats_static(const float* X, const float* scale_dev, int B_loc, int B, int row0,
+                             float* row_lse /*[B_loc]*/, float* col_max /*[B]*/, float* col_sum /*[B]*/,
+                             float* diag /*[B_loc]*/, void* stream);
 /*
  * Gradient pass: dX[m,k] = coef * scale * (exp(scale*X - row_lse[m]) + exp(scale*X - col_lse[k]) - 2*delta)
  * with coef = *coef_dev / (2B); dscale_partial += sum(dX/scale * X) (one float, atomically added).
