@@ -41,7 +41,7 @@ WORKLOADS = {
 METRIC = "MaxSim-loss fwd+bwd image-text pairs/sec"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE K1 launch, from an ncu capture of the same launch shape
 # (not measurable live): (workload, n_gpus) -> (bytes, source file under profiles/)
-PROFILED_K1_TRAFFIC = {("cfg2", 1): (6771814875392 + 94268055040, "profiles/r2a_k1_cfg2_dram.csv")}
+PROFILED_K1_TRAFFIC = {("cfg2", 1): (3658640584704 + 94227708672, "profiles/r4k_k1_cfg2_dram.csv")}   # image blocks of 192
 
 
 def peaks():

@@ -61,6 +61,8 @@ struct FwdTcParams {
   // pack_g * P exactly.  Tile t of a group starts at flat patch row pack_start[t] of the group and is pack_n[t]
   // wide: image t from its column pack_start[t] - t*P on, followed by the first (< 16) columns of image t + 1,
   // whose running max is carried into the next tile.  0 = padded tiles.
+  int l2_hint;           // pair kernel: bit0 = TMA loads carry L2 hints (image tiles evict_last, text tiles evict_first),
+                         // bit1 = argmax bytes are stored with the streaming (.cs) qualifier
   int pack_g;
   uint16_t pack_start[16];
   uint16_t pack_n[16];
@@ -424,6 +426,10 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
     uint32_t phase = 0;
     uint32_t a_phase = 0;
     const uint32_t a_full = smem_u32(&bars->a_full);
+    // L2 residency: the image block every cluster sweeps is re-read by all waves of units (keep it), a text tile is
+    // read once per block by one CTA (let it pass through)
+    const bool hinted = (p.l2_hint & 1) != 0;
+    const uint64_t pol_img = l2_policy_evict_last(), pol_txt = l2_policy_evict_first();
     for (int unit = cluster_id; unit < p.num_units; unit += num_clusters) {
       const int chunk = unit / p.num_m_tiles;            // num_m_tiles counts 256-row PAIRS here
       const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
@@ -431,8 +437,10 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
       mbar_wait(smem_u32(&bars->a_empty), a_phase ^ 1);        // previous unit's MMAs are done with A
       if (rank == 0) mbar_arrive_expect_tx(a_full, 2 * p.num_kb * kABlockBytes);
-      for (int kb = 0; kb < p.num_kb; ++kb)
-        tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
+      for (int kb = 0; kb < p.num_kb; ++kb) {
+        if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM, pol_txt);
+        else tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
+      }
       a_phase ^= 1;
       for (int j = j0; j < j1; ++j) {
         int row0 = j * p.p_stride + static_cast<int>(rank) * half_rows;
@@ -444,7 +452,8 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           mbar_wait(smem_u32(&bars->b_empty[stage]), phase ^ 1);
           const uint32_t full = smem_u32(&bars->b_full[stage]);
           if (rank == 0) mbar_arrive_expect_tx(full, 2 * p.b_block_bytes);
-          tma_load_2d_2cta(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0);
+          if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0, pol_img);
+          else tma_load_2d_2cta(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0);
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -602,6 +611,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           if (valid && p.argmax != nullptr) {
             const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
             if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
+            else if (p.l2_hint & 2) __stcs(reinterpret_cast<unsigned char*>(p.argmax) + off, static_cast<unsigned char>(bidx));
             else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
           }
           float v = valid ? best : 0.f;
@@ -797,6 +807,10 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       }
       chunks2 = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
       q.num_units = chunks2 * q.num_m_tiles;
+      {
+        static const int hint_env = getenv("CXL_K1_L2HINT") ? atoi(getenv("CXL_K1_L2HINT")) : 0;
+        q.l2_hint = hint_env;
+      }
       q.mean_mode = mean_mode;
       q.argmax_u16 = P > 256;
       q.S = S; q.cnt = cnt; q.argmax = argmax; q.ld_arg = ld_arg; q.dbg = nullptr;

@@ -66,6 +66,6 @@ head = TokenHead(256, 256).to(dev)
 with torch.autocast("cuda", dtype=torch.bfloat16):
     head(torch.randn(5, 7, 256, device=dev, generator=g))
 from colxlip_b200.retrieval import compute_retrieval                 # noqa: E402
-compute_retrieval(torch.randn(50, 50, device=dev, generator=g), {i: [i] for i in range(50)}, {i: i for i in range(50)})
+compute_retrieval(torch.randn(50, 50, device=dev, generator=g), {i: i for i in range(50)}, {i: [i] for i in range(50)})
 torch.cuda.synchronize()
 print("sanitize_probe: all launches finished, kernels launched:", lib.cxl_kernel_launches())
