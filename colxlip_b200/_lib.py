@@ -18,6 +18,7 @@ CXL_DTYPE_BF16 = 1
 CXL_DTYPE_F16 = 2
 CXL_MEAN_MASKED = 0
 CXL_MEAN_PLAIN = 1
+CXL_MEAN_ROUND16 = 0x10   # OR into mean_mode: row maxima rounded to the 16-bit operand dtype (autocast semantics)
 
 _lib: Optional[ctypes.CDLL] = None
 

@@ -135,7 +135,9 @@ int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int 
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
   if (static_cast<long long>(Bt) * T >= (1LL << 31) || static_cast<long long>(Bi) * P >= (1LL << 31))
     return CXL_ERR_UNSUPPORTED;
-  if (mean_mode != CXL_MEAN_MASKED && mean_mode != CXL_MEAN_PLAIN) return CXL_ERR_INVALID_ARG;
+  const int base_mode = mean_mode & ~CXL_MEAN_ROUND16;
+  if (base_mode != CXL_MEAN_MASKED && base_mode != CXL_MEAN_PLAIN) return CXL_ERR_INVALID_ARG;
+  if ((mean_mode & CXL_MEAN_ROUND16) && dtype == CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;   // fp32 einsum rounds nothing
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);

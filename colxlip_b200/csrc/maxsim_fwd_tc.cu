@@ -61,12 +61,19 @@ struct FwdTcParams {
   // pack_g * P exactly.  Tile t of a group starts at flat patch row pack_start[t] of the group and is pack_n[t]
   // wide: image t from its column pack_start[t] - t*P on, followed by the first (< 16) columns of image t + 1,
   // whose running max is carried into the next tile.  0 = padded tiles.
+  int round16;           // CXL_MEAN_ROUND16: row maxima are rounded to the operand dtype before they are summed (the
+                         // reference's autocast einsum hands torch.max 16-bit similarities, loss.py:34-35)
   int l2_hint;           // pair kernel: bit0 = TMA loads carry L2 hints (image tiles evict_last, text tiles evict_first),
                          // bit1 = argmax bytes are stored with the streaming (.cs) qualifier
   int pack_g;
   uint16_t pack_start[16];
   uint16_t pack_n[16];
 };
+
+// RN to bf16 / fp16 and back (NaN stays NaN): what a 16-bit einsum output holds
+__device__ __forceinline__ float round_to_16(float x, int f16) {
+  return f16 ? __half2float(__float2half_rn(x)) : __bfloat162float(__float2bfloat16_rn(x));
+}
 
 struct __align__(8) FwdTcBarriers {
   uint64_t b_full[kMaxStages];
@@ -341,6 +348,7 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
               else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
             }
+            if (p.round16) best = round_to_16(best, p.f16);
             float v = valid ? best : 0.f;
             float nz = (valid && best != 0.f) ? 1.f : 0.f;
 #pragma unroll
@@ -614,6 +622,7 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             else if (p.l2_hint & 2) __stcs(reinterpret_cast<unsigned char*>(p.argmax) + off, static_cast<unsigned char>(bidx));
             else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
           }
+          if (p.round16) best = round_to_16(best, p.f16);
           float v = valid ? best : 0.f;
           float nz = (valid && best != 0.f) ? 1.f : 0.f;
 #pragma unroll
@@ -710,9 +719,12 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
                   cudaStream_t stream) {
   if (D % kBlockK != 0 || D < kBlockK) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
+  const int round16 = (mean_mode & CXL_MEAN_ROUND16) ? 1 : 0;
+  mean_mode &= ~CXL_MEAN_ROUND16;
   if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
   FwdTcParams p;
   memset(&p, 0, sizeof(p));
+  p.round16 = round16;
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
   p.f16 = f16 ? 1 : 0;
   p.rows_a = Bt * T;

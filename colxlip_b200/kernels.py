@@ -12,10 +12,12 @@ from typing import Optional, Tuple
 import torch
 
 from . import _lib
-from ._lib import CXL_DTYPE_BF16, CXL_DTYPE_F16, CXL_DTYPE_F32, CXL_MEAN_MASKED, CXL_MEAN_PLAIN, check
+from ._lib import (CXL_DTYPE_BF16, CXL_DTYPE_F16, CXL_DTYPE_F32, CXL_MEAN_MASKED, CXL_MEAN_PLAIN, CXL_MEAN_ROUND16,
+                   check)
 
 MASKED = CXL_MEAN_MASKED
 MEAN = CXL_MEAN_PLAIN
+ROUND16 = CXL_MEAN_ROUND16
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -103,7 +105,7 @@ class CudaKernels:
         dev = _require_cuda(txt_op, img_op)
         Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
         S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
-        cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if mean_mode == MASKED else None
+        cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if (mean_mode & ~ROUND16) == MASKED else None
         argmax = self._alloc_argmax(Bt, Bi, T, P, dev) if save_argmax else None
         with torch.cuda.device(dev):
             check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, _PREC_DT[prec], mean_mode,

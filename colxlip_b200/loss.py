@@ -26,7 +26,7 @@ except ImportError:  # pragma: no cover
     has_distributed = False
     dist = None
 
-from .kernels import MASKED, MEAN, default_kernels
+from .kernels import MASKED, MEAN, ROUND16, default_kernels
 
 # "auto": tensor-core path in the 16-bit dtype torch.einsum would use at loss.py:34 -- the autocast dtype under CUDA
 # autocast (bf16, or fp16 for the reference's `--precision amp`, colxlip.sh:53 / train.py:131-134), else the
@@ -43,6 +43,27 @@ def set_precision(mode: str) -> None:
 
 def get_precision() -> str:
     return _PRECISION
+
+
+# Strict autocast arithmetic (off by default): under torch.autocast the reference's einsum (loss.py:34) returns 16-bit
+# similarities, so torch.max, the != 0 mask and the sum see row maxima ROUNDED to bf16 / fp16.  With the switch on K1
+# rounds every row maximum the same way (CXL_MEAN_ROUND16) and the scores agree with the reference's autocast pipeline
+# to fp32 summation order instead of to the 16-bit tolerance; off, the maxima stay in fp32 (closer to the fp32 oracle).
+_STRICT_AUTOCAST = os.environ.get("COLXLIP_B200_STRICT_AUTOCAST", "0") not in ("", "0")
+
+
+def set_strict_autocast(on: bool) -> None:
+    global _STRICT_AUTOCAST
+    _STRICT_AUTOCAST = bool(on)
+
+
+def get_strict_autocast() -> bool:
+    return _STRICT_AUTOCAST
+
+
+def _fwd_mode(mean_mode: int, prec: str) -> int:
+    """mean_mode as K1 takes it: + ROUND16 when strict autocast arithmetic is on and the operands are 16-bit"""
+    return (mean_mode | ROUND16) if (_STRICT_AUTOCAST and prec in ("bf16", "fp16")) else mean_mode
 
 
 def _auto_precision(*tensors: torch.Tensor) -> str:
@@ -93,7 +114,7 @@ class _MaxSimFn(torch.autograd.Function):
         need_grad = bool(grad_mode and (ctx.needs_input_grad[0] or ctx.needs_input_grad[1]))
         txt_op = k.prepare(txt_tok, T, prec)
         img_op = k.prepare(img_tok, k.img_row_stride(P, prec), prec)
-        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, mean_mode, need_grad)
+        S, cnt, argmax = k.maxsim_fwd(txt_op, img_op, T, P, prec, _fwd_mode(mean_mode, prec), need_grad)
         if need_grad:
             ctx.save_for_backward(txt_op, img_op, argmax, cnt)
         ctx.meta = (T, P, prec, mean_mode, k, img_tok.dtype, txt_tok.dtype)
@@ -247,11 +268,22 @@ def _global_rank(group, r: int) -> int:
     return dist.get_global_rank(group, r) if group is not None else r
 
 
+# K1 is a persistent kernel that fills every SM (one CTA with ~220 KB of shared memory each), so an NCCL kernel launched
+# while a K1 runs is not scheduled until that K1 drains -- on THIS rank, which stalls the same broadcast on every other
+# rank: with K1 started on the local shard while the remote ones were still in flight the ranks fell into a convoy
+# (8 x B200, cfg-2: forward 1867-2193 ms for 1410 ms of K1 launches, another 330-550 ms of skew at the next collective;
+# profiles/r4m_bench_cfg2_8gpu_overlapped_gather.json).  The broadcasts move 5.8 GB per rank at cfg-2 (50 GB at cfg-5):
+# tens of milliseconds over NVSwitch against 1.4 s (32 s) of K1, so they now finish before the first K1 launch.
+# CXL_GATHER_OVERLAP=1 restores the overlapped schedule (for A/B).
+_OVERLAP_GATHER = os.environ.get("CXL_GATHER_OVERLAP", "0") not in ("", "0")
+
+
 def _gather_shards(x: torch.Tensor, world_size: int, rank: int, group):
     """Every rank's `x` as SEPARATE tensors (shard r = rank r's x; this rank's own is `x` itself, no copy), fetched by
-    one broadcast per home rank on a side stream: K1 starts on the local shard at once and takes each remote shard as
-    it lands (ready[r] is the CUDA event to wait for, None when nothing is pending), and the backward can free the
-    shards one by one.  Replaces all_gather of the reference's gather_features (loss.py:70-86) for the token operand."""
+    one broadcast per home rank on a side stream, so there is no [W*b, ...] concatenation and the backward can free
+    the shards one by one.  ready[r] is the CUDA event the consumer of shard r has to wait for (None: nothing pending
+    -- the default, the current stream already waits for all of them; see _OVERLAP_GATHER).  Replaces all_gather of
+    the reference's gather_features (loss.py:70-86) for the token operand."""
     shards = [x if r == rank else torch.empty_like(x) for r in range(world_size)]
     ready = [None] * world_size
     if world_size == 1:
@@ -262,10 +294,14 @@ def _gather_shards(x: torch.Tensor, world_size: int, rank: int, group):
         with torch.cuda.stream(comm):
             for r in range(world_size):
                 dist.broadcast(shards[r], src=_global_rank(group, r), group=group)
-                if r != rank:
+                if r != rank and _OVERLAP_GATHER:
                     ready[r] = torch.cuda.Event()
                     ready[r].record(comm)
-        x.record_stream(comm)
+        if _OVERLAP_GATHER:
+            x.record_stream(comm)
+        else:
+            main.wait_stream(comm)                   # all shards have landed before the first K1 launch (and before
+                                                     # anything on the current stream can free them)
     else:
         for r in range(world_size):
             dist.broadcast(shards[r], src=_global_rank(group, r), group=group)
@@ -357,8 +393,8 @@ class _ColClipLossFn(torch.autograd.Function):
         row0 = rank * b
         dev = token_image_features.device
 
-        # global features first (small collectives), then the token operand: one broadcast per home rank on a side
-        # stream (K4, forward half) -- K1 runs on the local shard while the remote ones arrive
+        # global features first (small collectives), then the token operand: one broadcast per home rank (K4, forward
+        # half), all landed before K1 starts (see _OVERLAP_GATHER)
         _mark("step_start", dev)
         g_txt = _round_like_gemm_input(text_features, prec)
         g_img = _all_gather_cat(_round_like_gemm_input(image_features, prec), W, group)
@@ -369,7 +405,7 @@ class _ColClipLossFn(torch.autograd.Function):
         need_bwd = bool(cfg.get("need_bwd", True))
         args = [None] * W
         if W == 1:
-            S, cnt, args[0] = k.maxsim_fwd(txt_op, shards[0], T, P, prec, MASKED, need_bwd)
+            S, cnt, args[0] = k.maxsim_fwd(txt_op, shards[0], T, P, prec, _fwd_mode(MASKED, prec), need_bwd)
         else:
             S = torch.empty((b, B), dtype=torch.float32, device=dev)
             cnt = torch.empty((b, B), dtype=torch.float32, device=dev)
@@ -377,7 +413,7 @@ class _ColClipLossFn(torch.autograd.Function):
                 r = (rank + i) % W                       # own shard first: nothing to wait for
                 if ready[r] is not None:
                     torch.cuda.current_stream(dev).wait_event(ready[r])
-                S_r, cnt_r, args[r] = k.maxsim_fwd(txt_op, shards[r], T, P, prec, MASKED, need_bwd)
+                S_r, cnt_r, args[r] = k.maxsim_fwd(txt_op, shards[r], T, P, prec, _fwd_mode(MASKED, prec), need_bwd)
                 S[:, r * b:(r + 1) * b] = S_r
                 cnt[:, r * b:(r + 1) * b] = cnt_r
                 del S_r, cnt_r

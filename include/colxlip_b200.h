@@ -39,6 +39,11 @@ extern "C" {
 
 #define CXL_MEAN_MASKED 0 /* loss.py:38-44  sum / (count(max != 0) + 1e-8) */
 #define CXL_MEAN_PLAIN 1  /* model.py:628   mean over all T tokens          */
+/* OR into mean_mode of cxl_maxsim_fwd (16-bit dtypes only): every row maximum is rounded to the operand dtype (RN)
+ * before it enters the sum and the != 0 test -- the arithmetic of the reference under torch.autocast, whose einsum
+ * (loss.py:34) returns bf16 / fp16 similarities to torch.max while `sum` and the division run in fp32.  The argmax is
+ * unchanged: the fp32 maximum is always one of the patches that tie at 16-bit resolution. */
+#define CXL_MEAN_ROUND16 0x10
 
 const char* cxl_strerror(int code);
 

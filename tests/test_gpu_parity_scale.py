@@ -198,6 +198,48 @@ def test_argmax_vs_reference_pipeline_under_cuda_bf16_autocast(K):
           f"all within {worst_ulps:.3f} bf16 ulp")
 
 
+@pytest.mark.parametrize("dt", [torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+def test_strict_autocast_mode_reproduces_the_16bit_maxima(K, dt):
+    """CXL_MEAN_ROUND16 / set_strict_autocast: the reference under autocast sums row maxima that the einsum already
+    rounded to the autocast dtype (loss.py:34-35).  With the flag the scores agree with that pipeline to fp32 summation
+    order (plus the rare maximum whose fp32 value sits on a 16-bit rounding boundary and lands one step apart between
+    two accumulation orders), ~100x closer than the 16-bit tolerance the default mode is held to; cnt and the argmax
+    do not change."""
+    from colxlip_b200 import compute_colbert_similarity, set_strict_autocast
+    from colxlip_b200.kernels import ROUND16
+    Bt, Bi, T, P, D = 256, 192, 77, 196, 512
+    _, _, ti, tt = _device_inputs(Bi, P, T, D, seed=99, Bt=Bt)
+    prec = "bf16" if dt == torch.bfloat16 else "fp16"
+    ti, tt = ti.to(dt).float(), tt.to(dt).float()
+    txt_op, img_op = K.prepare(tt, T, prec), K.prepare(ti, K.img_row_stride(P, prec), prec)
+    S0, cnt0, arg0 = K.maxsim_fwd(txt_op, img_op, T, P, prec, O.MASKED, True)
+    S1, cnt1, arg1 = K.maxsim_fwd(txt_op, img_op, T, P, prec, O.MASKED | ROUND16, True)
+    assert torch.equal(arg0, arg1) and torch.equal(cnt0, cnt1)
+    S = torch.empty(Bt, Bi, device="cuda")
+    with torch.no_grad(), torch.autocast("cuda", dtype=dt):
+        for m0 in range(0, Bt, 32):
+            sim = torch.einsum('mnd,kqd->mknq', tt[m0:m0 + 32], ti)
+            assert sim.dtype == dt
+            mx = sim.max(dim=3)[0]
+            S[m0:m0 + 32] = torch.sum(mx, dim=2) / (torch.sum((mx != 0).float(), dim=2) + 1e-8)
+    scale = S.abs().max().item()
+    err_strict = (S1 - S).abs().max().item() / scale
+    err_default = (S0 - S).abs().max().item() / scale
+    assert err_strict <= 1e-4, err_strict
+    assert err_default > 3 * err_strict            # the default mode differs by the 16-bit rounding of the maxima
+    # the same through the public API switch (forward under autocast, both directions of the switch)
+    try:
+        set_strict_autocast(True)
+        with torch.autocast("cuda", dtype=dt):
+            Sp = compute_colbert_similarity(ti, tt)
+    finally:
+        set_strict_autocast(False)
+    torch.testing.assert_close(Sp.float(), S1, rtol=1e-6, atol=1e-7)
+    # fp32 operands do not take the flag
+    with pytest.raises(Exception):
+        K.maxsim_fwd(tt, ti, T, P, "fp32", O.MASKED | ROUND16, False)
+
+
 def test_rank_kernel_rejects_out_of_range_targets(K):
     """a stale / sentinel gallery index must not be dereferenced: rank -1 from the kernel, IndexError
     from compute_retrieval (what the reference's torch.where(...)[0][0] raises)."""
