@@ -36,6 +36,9 @@ SYMBOLS = {
     "cxl_pack_bf16": (c_int, [c_void_p, c_int, c_longlong, c_longlong, c_int, c_int, c_int, c_int, c_void_p, c_void_p]),
     "cxl_maxsim_fwd": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
                                c_void_p, c_void_p, c_void_p, c_void_p]),
+    "cxl_maxsim_fwd_workspace_bytes": (c_size_t, [c_int, c_int, c_int, c_int]),
+    "cxl_maxsim_fwd_ws": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int, c_int, c_void_p, c_void_p,
+                                  c_void_p, c_void_p, c_size_t, c_void_p]),
     "cxl_pair_weights": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_longlong, c_void_p, c_void_p]),
     "cxl_maxsim_bwd": (c_int, [c_void_p, c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_int, c_int,
                                c_int, c_int, c_void_p, c_void_p, c_int, c_void_p]),

@@ -31,9 +31,11 @@ int num_sms() {
 int img_row_stride(int P);
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
                   float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, int f16,
-                  cudaStream_t stream);
+                  cudaStream_t stream, float* S_extra = nullptr);
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream);
+                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream, float* S_extra = nullptr);
+int maxsim_fwd_slots(int T, int slot_rows);
+int maxsim_fwd_f32_slot_rows();
 int maxsim_bwd(const void* txt, const void* img, const void* argmax, long long ld_arg, long long arg_row_off,
                const float* w, int Bt, int Bi, int T, int P, int D, int dtype, int p_stride, int ld_pairs, int k_off,
                float* dtxt, int accumulate_txt, float* dimg, int accumulate_img, int force_generic, void* ws,
@@ -129,8 +131,8 @@ int cxl_pack_operand(const void* src, int src_dtype, long long src_item_stride, 
                       static_cast<cudaStream_t>(stream));
 }
 
-int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
-                   float* S, float* cnt, void* argmax, void* stream) {
+static int maxsim_fwd_entry(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
+                            float* S, float* cnt, void* argmax, void* ws, size_t ws_bytes, void* stream) {
   if (txt == nullptr || img == nullptr || S == nullptr) return CXL_ERR_INVALID_ARG;
   if (Bt <= 0 || Bi <= 0 || T <= 0 || P <= 0 || D <= 0) return CXL_ERR_INVALID_ARG;
   if (static_cast<long long>(Bt) * T >= (1LL << 31) || static_cast<long long>(Bi) * P >= (1LL << 31))
@@ -138,21 +140,45 @@ int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int 
   const int base_mode = mean_mode & ~CXL_MEAN_ROUND16;
   if (base_mode != CXL_MEAN_MASKED && base_mode != CXL_MEAN_PLAIN) return CXL_ERR_INVALID_ARG;
   if ((mean_mode & CXL_MEAN_ROUND16) && dtype == CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;   // fp32 einsum rounds nothing
+  if (dtype != CXL_DTYPE_BF16 && dtype != CXL_DTYPE_F16 && dtype != CXL_DTYPE_F32) return CXL_ERR_INVALID_ARG;
+  float* S_extra = nullptr;                              // ws given: fixed-order sums, S is slot 0 and ws holds the others
+  if (ws != nullptr) {
+    if (ws_bytes < cxl_maxsim_fwd_workspace_bytes(Bt, Bi, T, dtype)) return CXL_ERR_WORKSPACE;
+    if ((reinterpret_cast<uintptr_t>(ws) & 3) != 0) return CXL_ERR_INVALID_ARG;
+    S_extra = static_cast<float*>(ws);
+  }
   int rc = device_ok();
   if (rc != CXL_OK) return rc;
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const long long ld_arg = cxl_argmax_ld(Bt, T);
   if (dtype == CXL_DTYPE_BF16 || dtype == CXL_DTYPE_F16)
     rc = maxsim_fwd_tc(txt, img, Bt, Bi, T, P, D, mean_mode, S, cnt, argmax, ld_arg, nullptr, 0, 0,
-                       dtype == CXL_DTYPE_F16, st);
-  else if (dtype == CXL_DTYPE_F32)
-    rc = maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
-                        cnt, argmax, ld_arg, st);
+                       dtype == CXL_DTYPE_F16, st, S_extra);
   else
-    return CXL_ERR_INVALID_ARG;
+    rc = maxsim_fwd_f32(static_cast<const float*>(txt), static_cast<const float*>(img), Bt, Bi, T, P, D, mean_mode, S,
+                        cnt, argmax, ld_arg, st, S_extra);
   if (rc != CXL_OK) return rc;
   // torch.max propagates NaN, the epilogue's running max does not: scores of texts / images with a non-finite element -> NaN
   return poison_nonfinite(txt, img, Bt, Bi, T, dtype == CXL_DTYPE_F32 ? P : img_row_stride(P), D, dtype, S, st);
+}
+
+int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
+                   float* S, float* cnt, void* argmax, void* stream) {
+  return maxsim_fwd_entry(txt, img, Bt, Bi, T, P, D, dtype, mean_mode, S, cnt, argmax, nullptr, 0, stream);
+}
+
+size_t cxl_maxsim_fwd_workspace_bytes(int Bt, int Bi, int T, int dtype) {
+  if (Bt <= 0 || Bi <= 0 || T <= 0) return 0;
+  const int slot_rows = dtype == CXL_DTYPE_F32 ? maxsim_fwd_f32_slot_rows() : 32;
+  const size_t extra = static_cast<size_t>(maxsim_fwd_slots(T, slot_rows) - 1);
+  const size_t bytes = extra * static_cast<size_t>(Bt) * Bi * sizeof(float);
+  return bytes > 0 ? bytes : 4;                          // T = 1: a text never spans two blocks; keep ws != NULL meaningful
+}
+
+int cxl_maxsim_fwd_ws(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype, int mean_mode,
+                      float* S, float* cnt, void* argmax, void* ws, size_t ws_bytes, void* stream) {
+  if (ws == nullptr) return CXL_ERR_WORKSPACE;
+  return maxsim_fwd_entry(txt, img, Bt, Bi, T, P, D, dtype, mean_mode, S, cnt, argmax, ws, ws_bytes, stream);
 }
 
 int cxl_pair_weights(const float* dS, const float* cnt, const float* gscale_dev, int mean_mode, int T, long long n,

@@ -18,6 +18,8 @@ struct FwdF32Params {
   int imgs_per_cta;
   float* S;
   float* cnt;
+  float* S_extra;      // fixed-order sums (see maxsim_fwd_tc.cu): slots 1.. of the per-FM-row-block partials, or null (atomics)
+  long long slot_stride;
   void* argmax;
   long long ld_arg;
   int argmax_u16;
@@ -125,7 +127,12 @@ maxsim_fwd_f32_kernel(const FwdF32Params p) {
             nz += (v != 0.f) ? 1.f : 0.f;
           }
           const size_t pi = static_cast<size_t>(m) * p.Bi + k;
-          atomicAdd(p.S + pi, s);
+          if (p.S_extra != nullptr) {
+            const int slot = row0 / FM - (m * p.T) / FM;               // one writer per (slot, text, image)
+            (slot == 0 ? p.S : p.S_extra + static_cast<size_t>(slot - 1) * p.slot_stride)[pi] = s;
+          } else {
+            atomicAdd(p.S + pi, s);
+          }
           if (p.cnt != nullptr) atomicAdd(p.cnt + pi, nz);
         }
       }
@@ -134,9 +141,12 @@ maxsim_fwd_f32_kernel(const FwdF32Params p) {
 }
 
 int launch_maxsim_finalize(float* S, const float* cnt, size_t npairs, int T, int mean_mode, cudaStream_t stream);
+int launch_maxsim_finalize_slots(float* S, const float* S_extra, const float* cnt, int Bt, int Bi, int T, int slot_rows,
+                                 int mean_mode, cudaStream_t stream);
+int maxsim_fwd_f32_slot_rows() { return FM; }
 
 int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
-                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream) {
+                   float* cnt, void* argmax, long long ld_arg, cudaStream_t stream, float* S_extra) {
   if (D % 4 != 0) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
   if (mean_mode == CXL_MEAN_MASKED && cnt == nullptr) return CXL_ERR_INVALID_ARG;
@@ -144,6 +154,7 @@ int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, in
   p.txt = txt; p.img = img; p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
   p.rows_a = Bt * T;
   p.S = S; p.cnt = cnt; p.argmax = argmax; p.ld_arg = ld_arg; p.argmax_u16 = P > 256;
+  p.S_extra = S_extra; p.slot_stride = static_cast<long long>(Bt) * Bi;
   const int m_tiles = (p.rows_a + FM - 1) / FM;
   const int sms = num_sms();
   int chunks = (4 * sms + m_tiles - 1) / m_tiles;
@@ -153,11 +164,12 @@ int maxsim_fwd_f32(const float* txt, const float* img, int Bt, int Bi, int T, in
   p.imgs_per_cta = (Bi + chunks - 1) / chunks;
   chunks = (Bi + p.imgs_per_cta - 1) / p.imgs_per_cta;
   const size_t npairs = static_cast<size_t>(Bt) * Bi;
-  CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
+  if (S_extra == nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
   if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs * sizeof(float), stream));
   dim3 grid(m_tiles, chunks);
   maxsim_fwd_f32_kernel<<<grid, 256, 0, CXL_COUNTED(stream)>>>(p);
   CXL_CUDA_CHECK(cudaGetLastError());
+  if (S_extra != nullptr) return launch_maxsim_finalize_slots(S, S_extra, cnt, Bt, Bi, T, FM, mean_mode, stream);
   return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);
 }
 

@@ -44,7 +44,12 @@ struct FwdTcParams {
   int mean_mode;
   int argmax_u16;
   int f16;               // operands are fp16 instead of bf16 (same tiles, same rate; instruction descriptor formats differ)
-  float* S;              // [Bt,Bi] pre-zeroed accumulator of row maxima sums
+  float* S;              // [Bt,Bi] accumulator of row maxima sums: pre-zeroed and added to atomically, or (S_extra != null)
+                         // slot 0 of the fixed-order partial sums
+  float* S_extra;        // deterministic sums: slots 1.. of the per-32-row-block partial sums of a text, [nslots-1][Bt*Bi];
+                         // the block that holds rows R..R+31 of text m STORES its partial into slot (R>>5) - ((m*T)>>5)
+                         // (exactly one writer per cell), the finalize kernel adds a text's slots in ascending order
+  long long slot_stride; // Bt*Bi
   float* cnt;            // [Bt,Bi] pre-zeroed count of non-zero maxima (or null)
   void* argmax;          // [Bi][ld_arg] image-major (row = flat text-token index) or null
   long long ld_arg;
@@ -358,7 +363,13 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
               if (same & (1u << o)) { v += tv; nz += tn; }
             }
             if (head) {
-              atomicAdd(p.S + pair_base + k, v);
+              if (p.S_extra != nullptr) {
+                const int slot = (R >> 5) - ((m * p.T) >> 5);
+                float* dst = slot == 0 ? p.S : p.S_extra + static_cast<size_t>(slot - 1) * p.slot_stride;
+                dst[pair_base + k] = v;
+              } else {
+                atomicAdd(p.S + pair_base + k, v);
+              }
               if (p.cnt != nullptr) atomicAdd(p.cnt + pair_base + k, nz);
             }
           }
@@ -552,6 +563,11 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const bool head = valid && (lane == 0 || m_prev != m);
       float* s_row = p.S + static_cast<size_t>(m) * p.Bi;
       float* c_row = p.cnt != nullptr ? p.cnt + static_cast<size_t>(m) * p.Bi : nullptr;
+      float* s_slot = nullptr;
+      if (p.S_extra != nullptr) {
+        const int slot = (R >> 5) - ((m * p.T) >> 5);
+        s_slot = slot == 0 ? s_row : p.S_extra + static_cast<size_t>(slot - 1) * p.slot_stride + static_cast<size_t>(m) * p.Bi;
+      }
 
       for (int k = j0; k < j1; ++k) {                     // one image per tile
         mbar_wait(smem_u32(&bars->tmem_full[buf]), acc_phase);
@@ -632,7 +648,8 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             if (same & (1u << o2)) { v += tv; nz += tn; }
           }
           if (head) {
-            atomicAdd(s_row + k, v);
+            if (s_slot != nullptr) s_slot[k] = v;          // fixed-order sums: this block's own slot, one writer
+            else atomicAdd(s_row + k, v);
             if (c_row != nullptr) atomicAdd(c_row + k, nz);
           }
         }
@@ -660,6 +677,37 @@ __global__ void maxsim_finalize_kernel(float* __restrict__ S, const float* __res
     const float s = S[i];
     S[i] = (mean_mode == CXL_MEAN_MASKED) ? s / (cnt[i] + 1e-8f) : s * inv_T;
   }
+}
+
+// the same with the fixed-order slot sums in front: S[m,k] = slot0 + slot1 + ... over the 32-row (slot_rows-row) blocks
+// text m touches, ascending -- every run adds the same numbers in the same order
+__global__ void maxsim_finalize_slots_kernel(float* __restrict__ S, const float* __restrict__ S_extra,
+                                             const float* __restrict__ cnt, int Bt, int Bi, int T, int slot_rows,
+                                             float inv_T, int mean_mode) {
+  const size_t n = static_cast<size_t>(Bt) * Bi;
+  for (int m = blockIdx.y; m < Bt; m += gridDim.y) {
+    const int last = (m * T + T - 1) / slot_rows - (m * T) / slot_rows;      // highest slot text m wrote
+    for (int k = blockIdx.x * blockDim.x + threadIdx.x; k < Bi; k += gridDim.x * blockDim.x) {
+      const size_t i = static_cast<size_t>(m) * Bi + k;
+      float s = S[i];
+      for (int sl = 1; sl <= last; ++sl) s += S_extra[static_cast<size_t>(sl - 1) * n + i];
+      S[i] = (mean_mode == CXL_MEAN_MASKED) ? s / (cnt[i] + 1e-8f) : s * inv_T;
+    }
+  }
+}
+
+int maxsim_fwd_slots(int T, int slot_rows) { return (T + slot_rows - 2) / slot_rows + 1; }
+
+int launch_maxsim_finalize_slots(float* S, const float* S_extra, const float* cnt, int Bt, int Bi, int T, int slot_rows,
+                                 int mean_mode, cudaStream_t stream) {
+  if (Bt <= 0 || Bi <= 0) return CXL_OK;
+  int gx = (Bi + 255) / 256;
+  if (gx > 64) gx = 64;
+  dim3 g(gx, Bt > 65535 ? 65535 : Bt);
+  maxsim_finalize_slots_kernel<<<g, 256, 0, CXL_COUNTED(stream)>>>(S, S_extra, cnt, Bt, Bi, T, slot_rows,
+                                                                  1.0f / static_cast<float>(T), mean_mode);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
 }
 
 int launch_maxsim_finalize(float* S, const float* cnt, size_t npairs, int T, int mean_mode, cudaStream_t stream) {
@@ -716,7 +764,7 @@ int img_row_stride(int P) { return P <= 128 ? round_up(P, 8) : P; }
 
 int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int mean_mode, float* S,
                   float* cnt, void* argmax, long long ld_arg, float* dbg, int force_stream_a, int force_grid, int f16,
-                  cudaStream_t stream) {
+                  cudaStream_t stream, float* S_extra) {
   if (D % kBlockK != 0 || D < kBlockK) return CXL_ERR_UNSUPPORTED;
   if (P > 65535) return CXL_ERR_UNSUPPORTED;
   const int round16 = (mean_mode & CXL_MEAN_ROUND16) ? 1 : 0;
@@ -725,6 +773,8 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   FwdTcParams p;
   memset(&p, 0, sizeof(p));
   p.round16 = round16;
+  p.S_extra = S_extra;                                   // null: atomic sums; else the extra slots of the fixed-order sums
+  p.slot_stride = static_cast<long long>(Bt) * Bi;
   p.Bt = Bt; p.Bi = Bi; p.T = T; p.P = P; p.D = D;
   p.f16 = f16 ? 1 : 0;
   p.rows_a = Bt * T;
@@ -835,7 +885,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       rc2 = make_tmap(&tmB2, img, static_cast<long long>(Bi) * q.p_stride, D, q.n_tile / 2, p.f16);
       if (rc2 != CXL_OK) return rc2;
       const size_t npairs2 = static_cast<size_t>(Bt) * Bi;
-      CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
+      if (S_extra == nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
       if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs2 * sizeof(float), stream));
       if (overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem > max_smem) q.num_stages -= 1;
       const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem;
@@ -843,6 +893,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       int ncl = q.num_units < clusters ? q.num_units : clusters;
       maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
       CXL_CUDA_CHECK(cudaGetLastError());
+      if (S_extra != nullptr) return launch_maxsim_finalize_slots(S, S_extra, cnt, Bt, Bi, T, 32, mean_mode, stream);
       return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
     }
   }
@@ -882,7 +933,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   if (rc != CXL_OK) return rc;
 
   const size_t npairs = static_cast<size_t>(Bt) * Bi;
-  CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
+  if (S_extra == nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs * sizeof(float), stream));
   if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs * sizeof(float), stream));
 
   CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
@@ -891,6 +942,7 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
   maxsim_fwd_tc_kernel<<<grid, kThreads, smem_bytes, CXL_COUNTED(stream)>>>(tmA, tmB, p);
   CXL_CUDA_CHECK(cudaGetLastError());
 
+  if (S_extra != nullptr) return launch_maxsim_finalize_slots(S, S_extra, cnt, Bt, Bi, T, 32, mean_mode, stream);
   return launch_maxsim_finalize(S, cnt, npairs, T, mean_mode, stream);
 }
 

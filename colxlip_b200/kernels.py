@@ -7,6 +7,7 @@ nothing in this package falls back to CPU.
 """
 from __future__ import annotations
 
+import os
 from typing import Optional, Tuple
 
 import torch
@@ -18,6 +19,8 @@ from ._lib import (CXL_DTYPE_BF16, CXL_DTYPE_F16, CXL_DTYPE_F32, CXL_MEAN_MASKED
 MASKED = CXL_MEAN_MASKED
 MEAN = CXL_MEAN_PLAIN
 ROUND16 = CXL_MEAN_ROUND16
+# scores summed in a fixed order (cxl_maxsim_fwd_ws) unless CXL_S_ATOMIC=1 asks for the atomicAdd path of cxl_maxsim_fwd
+DETERMINISTIC_SCORES = os.environ.get("CXL_S_ATOMIC", "0") in ("", "0")
 
 
 def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
@@ -101,15 +104,27 @@ class CudaKernels:
 
     # ---- K1 --------------------------------------------------------------------------------------
     def maxsim_fwd(self, txt_op: torch.Tensor, img_op: torch.Tensor, T: int, P: int, prec: str, mean_mode: int,
-                   save_argmax: bool) -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor]]:
+                   save_argmax: bool, deterministic: Optional[bool] = None
+                   ) -> Tuple[torch.Tensor, Optional[torch.Tensor], Optional[torch.Tensor]]:
+        """deterministic (default: on unless CXL_S_ATOMIC=1): fixed-order sums of a text's row maxima through
+        cxl_maxsim_fwd_ws (a transient workspace of ((T+30)//32) * Bt * Bi floats) instead of atomicAdd."""
         dev = _require_cuda(txt_op, img_op)
         Bt, Bi, D = txt_op.shape[0], img_op.shape[0], txt_op.shape[2]
         S = torch.empty((Bt, Bi), dtype=torch.float32, device=dev)
         cnt = torch.empty((Bt, Bi), dtype=torch.float32, device=dev) if (mean_mode & ~ROUND16) == MASKED else None
         argmax = self._alloc_argmax(Bt, Bi, T, P, dev) if save_argmax else None
+        if deterministic is None:
+            deterministic = DETERMINISTIC_SCORES
         with torch.cuda.device(dev):
-            check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, _PREC_DT[prec], mean_mode,
-                                          _ptr(S), _ptr(cnt), _ptr(argmax), _stream()), "cxl_maxsim_fwd")
+            if deterministic:
+                nws = int(self.lib.cxl_maxsim_fwd_workspace_bytes(Bt, Bi, T, _PREC_DT[prec]))
+                ws = torch.empty(nws, dtype=torch.uint8, device=dev)
+                check(self.lib.cxl_maxsim_fwd_ws(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, _PREC_DT[prec], mean_mode,
+                                                 _ptr(S), _ptr(cnt), _ptr(argmax), _ptr(ws), nws, _stream()),
+                      "cxl_maxsim_fwd_ws")
+            else:
+                check(self.lib.cxl_maxsim_fwd(_ptr(txt_op), _ptr(img_op), Bt, Bi, T, P, D, _PREC_DT[prec], mean_mode,
+                                              _ptr(S), _ptr(cnt), _ptr(argmax), _stream()), "cxl_maxsim_fwd")
         return S, cnt, argmax
 
     # ---- K2 --------------------------------------------------------------------------------------

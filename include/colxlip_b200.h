@@ -91,6 +91,19 @@ int cxl_pack_operand(const void* src, int src_dtype, long long src_item_stride, 
 int cxl_img_row_stride(int P);
 int cxl_maxsim_fwd(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype,
                    int mean_mode, float* S, float* cnt, void* argmax, void* stream);
+/*
+ * The same with run-to-run reproducible scores (loss.py:38-44 sums a text's T maxima in one fixed order; torch's
+ * reduction is deterministic).  cxl_maxsim_fwd adds the partial sums of the 3-5 warps that hold one text's rows into
+ * S[m,k] with atomicAdd, so S can differ in its last bit between runs (cnt and the argmax cannot).  With a workspace
+ * every 32-row block (64-row for F32) STORES its partial sum of text m into its own slot -- slot = block index relative to the block
+ * that holds the text's first row, slot 0 is S itself, slots 1.. live in ws -- and the finalize kernel adds a text's
+ * slots in ascending order: same inputs, same bits, on every run and for every split of the images into calls.
+ * ws: cxl_maxsim_fwd_workspace_bytes(Bt, Bi, T, dtype) = ((T + 30) / 32) * Bt * Bi * 4 bytes for the 16-bit dtypes
+ * (12.9 GB at cfg-2 on one GPU, 0.8 GB per shard call at cfg-5), contents undefined on entry and on return.
+ */
+size_t cxl_maxsim_fwd_workspace_bytes(int Bt, int Bi, int T, int dtype);
+int cxl_maxsim_fwd_ws(const void* txt, const void* img, int Bt, int Bi, int T, int P, int D, int dtype,
+                      int mean_mode, float* S, float* cnt, void* argmax, void* ws, size_t ws_bytes, void* stream);
 
 /*
  * Per-pair backward weights  w[m,k] = dS[m,k] * g / (cnt[m,k] + 1e-8)   (CXL_MEAN_MASKED, loss.py:40-44)

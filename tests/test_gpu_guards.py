@@ -6,8 +6,8 @@ r1 #9 asked for its logs).  Two checks of our own, on small cases of every kerne
    i.e. no kernel wrote below or past any buffer it was given (TMA stores, vector stores of ragged tails, pad rows);
  * repeatability: the mbarrier / TMA-ring / cross-CTA commit protocols of K1 and K2 are run 6 times on the same
    inputs with different amounts of competing work on the GPU; argmax, cnt, dTxt and dImg must be bit-identical every
-   time (a missed wait or an early slot reuse shows up as a changed bit), S to fp32 rounding (its atomics are
-   order-free only up to rounding).
+   time (a missed wait or an early slot reuse shows up as a changed bit) -- S included, now that the default forward
+   entry (cxl_maxsim_fwd_ws) adds a text's partial sums in a fixed order.
 `-m gpu`."""
 import pytest
 import torch
@@ -166,6 +166,15 @@ def test_ring_and_barrier_protocols_repeat_bit_for_bit(monkeypatch, case):
         if ref is None:
             ref = cur
             continue
-        for name, x, y in zip(("argmax", "cnt", "dtxt", "dimg"), cur[:4], ref[:4]):
-            assert torch.equal(x, y), (name, rep)
-        torch.testing.assert_close(cur[4], ref[4], rtol=1e-6, atol=1e-7)
+        for name, x, y in zip(("argmax", "cnt", "dtxt", "dimg", "S"), cur, ref):
+            assert torch.equal(x, y), (name, rep)          # S too: cxl_maxsim_fwd_ws sums in a fixed order
+    # the atomicAdd entry (cxl_maxsim_fwd) agrees to fp32 rounding, and cnt / argmax exactly
+    S_a, cnt_a, arg_a = K.maxsim_fwd(txt_op, img_op, T, P, prec, O.MASKED, True, deterministic=False)
+    assert torch.equal(cnt_a, ref[1]) and torch.equal(arg_a[:, :Bt * T], ref[0])
+    torch.testing.assert_close(S_a, ref[4], rtol=1e-6, atol=1e-7)
+    # fixed order also means: any split of the images into calls gives the same bits
+    if Bi >= 2:
+        h = Bi // 2
+        S0, _, _ = K.maxsim_fwd(txt_op, img_op[:h].contiguous(), T, P, prec, O.MASKED, False)
+        S1, _, _ = K.maxsim_fwd(txt_op, img_op[h:].contiguous(), T, P, prec, O.MASKED, False)
+        assert torch.equal(torch.cat([S0, S1], dim=1), ref[4])
