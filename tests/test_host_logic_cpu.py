@@ -218,7 +218,7 @@ def _free_port():
 
 def _worker(rank, world, port, gather_with_grad, q, shard_dimg=False):
     if shard_dimg:
-        os.environ["CXL_DIMG_GATHER_MAX_GB"] = "0"      # force the one-home-rank-at-a-time dImg path (cfg-5 sized runs)
+        os.environ["CXL_DIMG_REDUCE_MB"] = "0.0005"     # dImg partials go home in pieces of one or two images (cfg-5 sized runs use bounded pieces)
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
