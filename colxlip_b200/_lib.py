@@ -62,6 +62,9 @@ SYMBOLS = {
                                          c_void_p]),
     "cxl_infonce_grad": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
                                  c_void_p, c_void_p, c_void_p]),
+    "cxl_infonce_grad_workspace_bytes": (c_size_t, [c_int, c_int]),
+    "cxl_infonce_grad_ws": (c_int, [c_void_p, c_void_p, c_void_p, c_int, c_int, c_int, c_void_p, c_void_p, c_void_p,
+                                    c_void_p, c_void_p, c_void_p, c_size_t, c_void_p]),
     "cxl_l2norm_fwd": (c_int, [c_void_p, c_int, c_longlong, c_int, c_void_p, c_int, c_void_p, c_void_p]),
     "cxl_l2norm_bwd": (c_int, [c_void_p, c_int, c_void_p, c_int, c_void_p, c_longlong, c_int, c_void_p, c_int, c_void_p]),
     "cxl_gemm_nt": (c_int, [c_void_p, c_void_p, c_int, c_int, c_int, c_int, c_void_p, c_longlong, c_void_p]),

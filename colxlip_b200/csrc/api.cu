@@ -50,7 +50,8 @@ int infonce_stats_static(const float* X, const float* scale_dev, int B_loc, int 
                          float* col_max, float* col_sum, float* diag, cudaStream_t stream);
 int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                  const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
-                 cudaStream_t stream);
+                 cudaStream_t stream, float* partials = nullptr);
+size_t infonce_grad_workspace_bytes(int B_loc, int B);
 int pack_bf16(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n, int n_pad,
               int D, void* dst, cudaStream_t stream);
 int pack_operand(const void* src, int src_dtype, long long item_stride, long long row_stride, int items, int n,
@@ -305,6 +306,20 @@ int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_d
   if (rc != CXL_OK) return rc;
   return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX, dscale_accum,
                       static_cast<cudaStream_t>(stream));
+}
+
+size_t cxl_infonce_grad_workspace_bytes(int B_loc, int B) { return infonce_grad_workspace_bytes(B_loc, B); }
+
+int cxl_infonce_grad_ws(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                        const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                        void* ws, size_t ws_bytes, void* stream) {
+  if (!X || !scale_dev || !coef_dev || !row_lse || !dX || !dscale_accum) return CXL_ERR_INVALID_ARG;  // col_lse may be null
+  if (ws == nullptr || ws_bytes < infonce_grad_workspace_bytes(B_loc, B)) return CXL_ERR_WORKSPACE;
+  if ((reinterpret_cast<uintptr_t>(ws) & 3) != 0) return CXL_ERR_INVALID_ARG;
+  int rc = device_ok();
+  if (rc != CXL_OK) return rc;
+  return infonce_grad(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX, dscale_accum,
+                      static_cast<cudaStream_t>(stream), static_cast<float*>(ws));
 }
 
 int cxl_l2norm_fwd(const void* x, int x_dtype, long long rows, int D, void* y, int y_dtype, float* inv_norm,

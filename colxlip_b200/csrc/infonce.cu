@@ -135,7 +135,8 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
                                                            const float* __restrict__ row_lse,
                                                            const float* __restrict__ col_lse,
                                                            const float* __restrict__ cnt, float* dX,
-                                                           float* __restrict__ dscale_accum) {
+                                                           float* __restrict__ dscale_accum,
+                                                           float* __restrict__ partials) {
   const int m = blockIdx.y;
   const float scale = *scale_p;
   const float coef = *coef_p / (2.f * static_cast<float>(B));
@@ -184,8 +185,26 @@ __global__ void __launch_bounds__(256) infonce_grad_kernel(const float* X, const
   if (threadIdx.x == 0) {
     float t = 0.f;
     for (int w = 0; w < (blockDim.x >> 5); ++w) t += part[w];
-    atomicAdd(dscale_accum, t);
+    // partials != null: this block's own cell, summed afterwards in a fixed order (reproducible d logit_scale)
+    if (partials != nullptr) partials[static_cast<size_t>(blockIdx.y) * gridDim.x + blockIdx.x] = t;
+    else atomicAdd(dscale_accum, t);
   }
+}
+
+// *accum += sum(partials[0..n)) in an order that depends only on n: thread t adds elements t, t + 1024, ... in
+// ascending order, then a fixed shared-memory tree
+__global__ void __launch_bounds__(1024) sum_fixed_order_kernel(const float* __restrict__ partials, size_t n,
+                                                               float* __restrict__ accum) {
+  __shared__ float sh[1024];
+  float t = 0.f;
+  for (size_t i = threadIdx.x; i < n; i += 1024) t += partials[i];
+  sh[threadIdx.x] = t;
+  __syncthreads();
+  for (int o = 512; o > 0; o >>= 1) {
+    if (static_cast<int>(threadIdx.x) < o) sh[threadIdx.x] += sh[threadIdx.x + o];
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) *accum += sh[0];
 }
 
 size_t infonce_workspace_bytes(int B_loc, int B) {
@@ -212,27 +231,44 @@ int infonce_stats(const float* X, const float* scale_dev, int B_loc, int B, int 
   return CXL_OK;
 }
 
+static int infonce_grad_grid_x(int B) {
+  int gx = (B + 256 * 8 - 1) / (256 * 8);
+  return gx < 1 ? 1 : gx;
+}
+
+size_t infonce_grad_workspace_bytes(int B_loc, int B) {
+  if (B_loc <= 0 || B <= 0) return 0;
+  return static_cast<size_t>(infonce_grad_grid_x(B)) * static_cast<size_t>(B_loc) * sizeof(float);
+}
+
+// partials: null = d logit_scale accumulated with atomicAdd; else one float per block (infonce_grad_workspace_bytes),
+// summed in a fixed order after the last slab
+static int infonce_grad_slab(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                             const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                             float* partials, cudaStream_t stream) {
+  dim3 g(infonce_grad_grid_x(B), B_loc);
+  infonce_grad_kernel<<<g, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX,
+                                             dscale_accum, partials);
+  CXL_CUDA_CHECK(cudaGetLastError());
+  return CXL_OK;
+}
+
 int infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                  const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
-                 cudaStream_t stream) {
+                 cudaStream_t stream, float* partials) {
   if (B_loc <= 0 || B <= 0 || row0 < 0 || row0 + B_loc > B) return CXL_ERR_INVALID_ARG;
-  if (B_loc > 65535) {
-    // grid.y limit: process in slabs of rows
-    for (int r = 0; r < B_loc; r += 65535) {
-      const int nr = min(65535, B_loc - r);
-      int rc = infonce_grad(X + static_cast<size_t>(r) * B, scale_dev, coef_dev, nr, B, row0 + r, row_lse + r, col_lse,
-                            cnt ? cnt + static_cast<size_t>(r) * B : nullptr, dX + static_cast<size_t>(r) * B,
-                            dscale_accum, stream);
-      if (rc != CXL_OK) return rc;
-    }
-    return CXL_OK;
+  const size_t gx = static_cast<size_t>(infonce_grad_grid_x(B));
+  for (int r = 0; r < B_loc; r += 65535) {               // grid.y limit: slabs of rows
+    const int nr = min(65535, B_loc - r);
+    int rc = infonce_grad_slab(X + static_cast<size_t>(r) * B, scale_dev, coef_dev, nr, B, row0 + r, row_lse + r, col_lse,
+                               cnt ? cnt + static_cast<size_t>(r) * B : nullptr, dX + static_cast<size_t>(r) * B,
+                               dscale_accum, partials ? partials + static_cast<size_t>(r) * gx : nullptr, stream);
+    if (rc != CXL_OK) return rc;
   }
-  int gx = (B + 256 * 8 - 1) / (256 * 8);
-  if (gx < 1) gx = 1;
-  dim3 g(gx, B_loc);
-  infonce_grad_kernel<<<g, 256, 0, CXL_COUNTED(stream)>>>(X, scale_dev, coef_dev, B_loc, B, row0, row_lse, col_lse, cnt, dX,
-                                             dscale_accum);
-  CXL_CUDA_CHECK(cudaGetLastError());
+  if (partials != nullptr) {
+    sum_fixed_order_kernel<<<1, 1024, 0, CXL_COUNTED(stream)>>>(partials, gx * static_cast<size_t>(B_loc), dscale_accum);
+    CXL_CUDA_CHECK(cudaGetLastError());
+  }
   return CXL_OK;
 }
 

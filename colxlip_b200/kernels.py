@@ -254,9 +254,16 @@ class CudaKernels:
         dX = torch.empty_like(X) if out is None else out
         dscale = torch.zeros(1, dtype=torch.float32, device=dev)
         with torch.cuda.device(dev):
-            check(self.lib.cxl_infonce_grad(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
-                                            _ptr(col_lse), _ptr(cnt), _ptr(dX), _ptr(dscale), _stream()),
-                  "cxl_infonce_grad")
+            if DETERMINISTIC_SCORES:                      # d logit_scale summed in a fixed order (per-block partials in ws)
+                nws = int(self.lib.cxl_infonce_grad_workspace_bytes(B_loc, B))
+                ws = torch.empty(max(nws, 4), dtype=torch.uint8, device=dev)
+                check(self.lib.cxl_infonce_grad_ws(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
+                                                   _ptr(col_lse), _ptr(cnt), _ptr(dX), _ptr(dscale), _ptr(ws), nws,
+                                                   _stream()), "cxl_infonce_grad_ws")
+            else:
+                check(self.lib.cxl_infonce_grad(_ptr(X), _ptr(scale), _ptr(coef), B_loc, B, row0, _ptr(row_lse),
+                                                _ptr(col_lse), _ptr(cnt), _ptr(dX), _ptr(dscale), _stream()),
+                      "cxl_infonce_grad")
         return dX, dscale
 
     # ---- producer side: L2 normalise + operand cast -----------------------------------

@@ -221,6 +221,13 @@ int cxl_infonce_stats_static(const float* X, const float* scale_dev, int B_loc, 
 int cxl_infonce_grad(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
                      const float* row_lse, const float* col_lse /*[B] global, or NULL*/, const float* cnt /*[B_loc,B] or NULL*/,
                      float* dX, float* dscale_accum, void* stream);
+/* The same with a reproducible d logit_scale: every block stores its partial of sum(dX/scale * X) into ws
+ * (cxl_infonce_grad_workspace_bytes: one float per block, 2 MB at B_loc = B = 32768) and one fixed-order pass adds them
+ * into *dscale_accum, instead of one atomicAdd per block.  dX is identical to cxl_infonce_grad's. */
+size_t cxl_infonce_grad_workspace_bytes(int B_loc, int B);
+int cxl_infonce_grad_ws(const float* X, const float* scale_dev, const float* coef_dev, int B_loc, int B, int row0,
+                        const float* row_lse, const float* col_lse, const float* cnt, float* dX, float* dscale_accum,
+                        void* ws, size_t ws_bytes, void* stream);
 
 /*
  * Global-embedding logits and their gradient GEMMs on the tcgen05 pipeline of cxl_maxsim_fwd (plain-GEMM epilogue).

@@ -178,3 +178,58 @@ def test_ring_and_barrier_protocols_repeat_bit_for_bit(monkeypatch, case):
         S0, _, _ = K.maxsim_fwd(txt_op, img_op[:h].contiguous(), T, P, prec, O.MASKED, False)
         S1, _, _ = K.maxsim_fwd(txt_op, img_op[h:].contiguous(), T, P, prec, O.MASKED, False)
         assert torch.equal(torch.cat([S0, S1], dim=1), ref[4])
+
+
+@pytest.mark.parametrize("autocast", [None, torch.bfloat16, torch.float16], ids=["fp32", "bf16", "fp16"])
+def test_loss_and_all_gradients_repeat_bit_for_bit(autocast):
+    """The whole step is reproducible: losses, the four feature gradients and d logit_scale (fixed-order sums in K1's
+    finalize and in cxl_infonce_grad_ws; no float atomics are left on the default path)."""
+    import contextlib
+    from colxlip_b200 import ClipLoss, ColClipLoss
+    B, P, T, D = 96, 196, 77, 256
+    inputs = [t.cuda() for t in O.synth_inputs(B, P, T, D, seed=31, pad_text=True)]
+    noise = torch.randn(2048, 2048, device="cuda")
+    side = torch.cuda.Stream()
+    runs = []
+    for rep in range(4):
+        if rep % 2:
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                for _ in range(3):
+                    noise = noise @ noise * 1e-4
+        xs = [t.clone().requires_grad_() for t in inputs]
+        ls = torch.tensor(1 / 0.07, device="cuda", requires_grad=True)
+        ctx = torch.autocast("cuda", dtype=autocast) if autocast is not None else contextlib.nullcontext()
+        with ctx:
+            out = ColClipLoss(alpha=0.5)(*xs, ls, output_dict=True)
+            extra = ClipLoss()(xs[0], xs[1], ls)
+        (out["total_loss"] + extra).backward()
+        torch.cuda.synchronize()
+        runs.append([out[k].detach().clone() for k in sorted(out)] + [extra.detach().clone()] +
+                    [x.grad.clone() for x in xs] + [ls.grad.clone()])
+    for r in runs[1:]:
+        for i, (a, b) in enumerate(zip(r, runs[0])):
+            assert torch.equal(a, b), i
+
+
+def test_infonce_grad_ws_matches_the_atomic_entry():
+    from colxlip_b200.kernels import CudaKernels
+    from colxlip_b200 import kernels as KM
+    K = CudaKernels()
+    g = torch.Generator(device="cuda").manual_seed(4)
+    X = torch.randn(300, 1000, device="cuda", generator=g) * 0.2
+    cnt = torch.randint(1, 78, (300, 1000), device="cuda", generator=g).float()
+    scale, coef = torch.tensor([14.0], device="cuda"), torch.tensor([0.5], device="cuda")
+    rl, cm, cs, _ = K.infonce_stats(X, scale, 100)
+    cl = cm + torch.log(cs)
+    assert KM.DETERMINISTIC_SCORES
+    d1, s1 = K.infonce_grad(X, scale, coef, 100, rl, cl, cnt=cnt)
+    d2, s2 = K.infonce_grad(X, scale, coef, 100, rl, cl, cnt=cnt)
+    assert torch.equal(d1, d2) and torch.equal(s1, s2)
+    try:
+        KM.DETERMINISTIC_SCORES = False
+        d3, s3 = K.infonce_grad(X, scale, coef, 100, rl, cl, cnt=cnt)
+    finally:
+        KM.DETERMINISTIC_SCORES = True
+    assert torch.equal(d1, d3)
+    torch.testing.assert_close(s1, s3, rtol=1e-5, atol=1e-7)
