@@ -41,7 +41,9 @@ WORKLOADS = {
 METRIC = "MaxSim-loss fwd+bwd image-text pairs/sec"
 # dram__bytes_read.sum + dram__bytes_write.sum of ONE K1 launch, from an ncu capture of the same launch shape
 # (not measurable live): (workload, n_gpus) -> (bytes, source file under profiles/)
-PROFILED_K1_TRAFFIC = {("cfg2", 1): (3658640584704 + 94227708672, "profiles/r4k_k1_cfg2_dram.csv")}   # image blocks of 192
+PROFILED_K1_TRAFFIC = {("cfg2", 1): (3658640584704 + 94227708672, "profiles/r4k_k1_cfg2_dram.csv"),   # image blocks of 192
+                       # the [4096 x 32768] launch the K1-alone leg times on each of 8 ranks
+                       ("cfg2", 8): (193990447872 + 11689009152, "profiles/r4j_k1_img_block_ncu.txt")}
 
 
 def peaks():
