@@ -8,7 +8,7 @@ import torch
 
 from oracle import colxlip_oracle as O
 
-MASKED, MEAN = 0, 1
+MASKED, MEAN, ROUND16 = 0, 1, 0x10
 
 
 class TorchRefKernels:
@@ -25,8 +25,11 @@ class TorchRefKernels:
             return x.to(torch.float16).float().contiguous()
         return x.float().contiguous()
 
-    def maxsim_fwd(self, txt_op, img_op, T, P, prec, mean_mode, save_argmax):
+    def maxsim_fwd(self, txt_op, img_op, T, P, prec, mean_mode, save_argmax, deterministic=None):
         mx, arg = O.maxsim_rowmax(img_op, txt_op)
+        if mean_mode & ROUND16:                                  # strict autocast arithmetic: 16-bit row maxima
+            mx = mx.to(torch.float16 if prec == "fp16" else torch.bfloat16).float()
+            mean_mode &= ~ROUND16
         if mean_mode == MASKED:
             cnt = (mx != 0).float().sum(dim=2)
             S = mx.sum(dim=2) / (cnt + 1e-8)

@@ -264,3 +264,35 @@ def test_world2_gloo_matches_global_batch(gather_with_grad, shard_dimg):
             g = torch.from_numpy(g)
             assert (g - ref).abs().max().item() <= 1e-5 * ref.abs().max().item() + 1e-8, (rank, n)
         assert abs(ls_grad - ref_grads["logit_scale"].item()) < 1e-5 * max(1e-3, abs(ref_grads["logit_scale"].item()))
+
+
+def test_strict_autocast_switch_reproduces_the_reference_under_cpu_autocast():
+    """set_strict_autocast: K1 is asked for 16-bit row maxima (mean_mode | ROUND16) exactly when the operands are 16-bit.
+    With the stand-in kernels the scores then equal the reference's own arithmetic under torch.autocast (einsum output
+    in bf16 before torch.max, loss.py:34-35; sum and division in fp32) up to fp32 summation order."""
+    from colxlip_b200.kernels import ROUND16
+    assert L._fwd_mode(0, "bf16") == 0 and L._fwd_mode(0, "fp32") == 0
+    _, _, ti, tt = _inputs(6, 10, 7, 64, 3)
+    ti, tt = ti.to(torch.bfloat16).float(), tt.to(torch.bfloat16).float()
+    k = TorchRefKernels()
+    try:
+        L.set_strict_autocast(True)
+        assert L.get_strict_autocast()
+        assert L._fwd_mode(0, "bf16") == ROUND16 and L._fwd_mode(1, "fp16") == (1 | ROUND16) and L._fwd_mode(0, "fp32") == 0
+        L.set_precision("bf16")
+        S_strict = L._maxsim(ti, tt, 0, k)
+    finally:
+        L.set_strict_autocast(False)
+        L.set_precision("auto")
+    L.set_precision("bf16")
+    try:
+        S_default = L._maxsim(ti, tt, 0, k)
+    finally:
+        L.set_precision("auto")
+    with torch.autocast("cpu", dtype=torch.bfloat16):
+        sim = torch.einsum('mnd,kqd->mknq', tt, ti)
+        assert sim.dtype == torch.bfloat16
+        mx = sim.max(dim=3)[0]
+        ref = torch.sum(mx.float(), dim=2) / (torch.sum((mx != 0).float(), dim=2) + 1e-8)
+    assert (S_strict - ref).abs().max().item() <= 2e-4 * ref.abs().max().item()
+    assert (S_default - ref).abs().max().item() > (S_strict - ref).abs().max().item()
