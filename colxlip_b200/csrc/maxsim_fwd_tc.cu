@@ -399,14 +399,20 @@ maxsim_fwd_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_const
 // CTA kernel, which is bound by the 128 B/clk shared-memory port (TMA writes + UMMA operand reads).
 // Barriers: the even CTA owns a_full / b_full (both CTAs' TMA loads credit them) and tmem_empty (8 epilogue
 // warps); b_empty / a_empty / tmem_full exist in both CTAs and are signalled by multicast tcgen05.commit.
-// Used for 128 < P <= 256 (one image per N tile); other geometries run the single-CTA kernel above.
+// SA = false: 128 < P <= 256 (one image per N tile) with a text tile that fits next to the ring.
+// SA = true ("streamed A"): the text tile does not stay resident (D = 768: 192 KB) or an image spans several N tiles
+// (P > 256: `parts` tiles of part_cols columns, running max carried from part to part).  A ring stage then holds this
+// CTA's [128 x 64] text block AND its half of the image block; per k-block and CTA the shared-memory port moves
+// 16 + 12 KB of TMA writes and 16 + 12 KB of operand reads (N = 192) against 16 + 24 and 16 + 24 KB in the single-CTA
+// kernel, which is what bounds that kernel at the cfg-5 geometry.
+template <bool SA>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(kThreads2, 1)
 maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                       const FwdTcParams p) {
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
   uint8_t* smem_a = smem;
-  uint8_t* smem_ring = smem + p.num_kb * kABlockBytes;
+  uint8_t* smem_ring = SA ? smem : smem + p.num_kb * kABlockBytes;
   FwdTcBarriers* bars = reinterpret_cast<FwdTcBarriers*>(smem_ring + p.num_stages * p.stage_bytes);
 
   const int warp = threadIdx.x >> 5;
@@ -454,25 +460,37 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int m_tile = (unit - chunk * p.num_m_tiles) * 2 + static_cast<int>(rank);
       const int j0 = chunk * p.tiles_per_unit;
       const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
-      mbar_wait(smem_u32(&bars->a_empty), a_phase ^ 1);        // previous unit's MMAs are done with A
-      if (rank == 0) mbar_arrive_expect_tx(a_full, 2 * p.num_kb * kABlockBytes);
-      for (int kb = 0; kb < p.num_kb; ++kb) {
-        if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM, pol_txt);
-        else tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
+      if constexpr (!SA) {
+        mbar_wait(smem_u32(&bars->a_empty), a_phase ^ 1);        // previous unit's MMAs are done with A
+        if (rank == 0) mbar_arrive_expect_tx(a_full, 2 * p.num_kb * kABlockBytes);
+        for (int kb = 0; kb < p.num_kb; ++kb) {
+          if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM, pol_txt);
+          else tma_load_2d_2cta(smem_u32(smem_a + kb * kABlockBytes), &tmA, a_full, kb * kBlockK, m_tile * kBlockM);
+        }
+        a_phase ^= 1;
       }
-      a_phase ^= 1;
       for (int j = j0; j < j1; ++j) {
         int row0 = j * p.p_stride + static_cast<int>(rank) * half_rows;
-        if (p.pack_g) {                                  // packed tiles: this CTA's half of tile t of group grp
+        if constexpr (SA) {                              // tile j = part (j % parts) of image j / parts
+          const int g = j / p.parts;
+          row0 = g * p.p_stride + (j - g * p.parts) * p.part_cols + static_cast<int>(rank) * half_rows;
+        } else if (p.pack_g) {                           // packed tiles: this CTA's half of tile t of group grp
           const int grp = j / p.pack_g, t = j - grp * p.pack_g;
           row0 = grp * p.pack_g * p.P + p.pack_start[t] + static_cast<int>(rank) * (p.pack_n[t] >> 1);
         }
         for (int kb = 0; kb < p.num_kb; ++kb) {
           mbar_wait(smem_u32(&bars->b_empty[stage]), phase ^ 1);
           const uint32_t full = smem_u32(&bars->b_full[stage]);
-          if (rank == 0) mbar_arrive_expect_tx(full, 2 * p.b_block_bytes);
-          if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0, pol_img);
-          else tma_load_2d_2cta(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0);
+          if constexpr (SA) {
+            if (rank == 0) mbar_arrive_expect_tx(full, 2 * (kABlockBytes + p.b_block_bytes));
+            const uint32_t st = smem_u32(smem_ring + stage * p.stage_bytes);
+            tma_load_2d_2cta(st, &tmA, full, kb * kBlockK, m_tile * kBlockM);
+            tma_load_2d_2cta(st + kABlockBytes, &tmB, full, kb * kBlockK, row0);
+          } else {
+            if (rank == 0) mbar_arrive_expect_tx(full, 2 * p.b_block_bytes);
+            if (hinted) tma_load_2d_2cta_hint(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0, pol_img);
+            else tma_load_2d_2cta(smem_u32(smem_ring + stage * p.stage_bytes), &tmB, full, kb * kBlockK, row0);
+          }
           if (++stage == p.num_stages) { stage = 0; phase ^= 1; }
         }
       }
@@ -497,8 +515,10 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
       const int chunk = unit / p.num_m_tiles;
       const int j0 = chunk * p.tiles_per_unit;
       const int j1 = min(j0 + p.tiles_per_unit, p.total_n_tiles);
-      mbar_wait(smem_u32(&bars->a_full), a_phase);
-      a_phase ^= 1;
+      if constexpr (!SA) {
+        mbar_wait(smem_u32(&bars->a_full), a_phase);
+        a_phase ^= 1;
+      }
       for (int j = j0; j < j1; ++j) {
         mbar_wait(smem_u32(&bars->tmem_empty[buf]), acc_phase ^ 1);   // both CTAs' epilogues drained this buffer
         tc_fence_after();
@@ -508,8 +528,9 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           mbar_wait(smem_u32(&bars->b_full[stage]), phase);
           tc_fence_after();
           if (elect_one()) {
-            const uint64_t da = desc_a0 + static_cast<uint64_t>(kb * a_step);
-            const uint64_t db = desc_b0 + static_cast<uint64_t>(stage * b_step);
+            const uint64_t da = SA ? desc_b0 + static_cast<uint64_t>(stage * b_step)       // text block at the head of the stage
+                                   : desc_a0 + static_cast<uint64_t>(kb * a_step);
+            const uint64_t db = desc_b0 + static_cast<uint64_t>(stage * b_step) + (SA ? (kABlockBytes >> 4) : 0);
 #pragma unroll
             for (int k = 0; k < kBlockK / kUmmaK; ++k)
               umma_bf16_2cta(tmem_d, da + 2 * k, db + 2 * k, idesc_j, (kb | k) != 0);   // +32 bytes per UMMA_K
@@ -523,8 +544,10 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         buf ^= 1;
         if (buf == 0) acc_phase ^= 1;
       }
-      if (elect_one()) umma_commit_2cta(smem_u32(&bars->a_empty), 3);
-      __syncwarp();
+      if constexpr (!SA) {
+        if (elect_one()) umma_commit_2cta(smem_u32(&bars->a_empty), 3);
+        __syncwarp();
+      }
     }
   } else if (warp >= 4) {
     // ===================== epilogue (both CTAs): max/argmax over patches, per-text sums =====================
@@ -569,13 +592,28 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
         s_slot = slot == 0 ? s_row : p.S_extra + static_cast<size_t>(slot - 1) * p.slot_stride + static_cast<size_t>(m) * p.Bi;
       }
 
-      for (int k = j0; k < j1; ++k) {                     // one image per tile
+      float run_best = -INFINITY;                         // SA: lower warp's running (max, argmax) over the parts of an image
+      int run_idx = 0;
+      for (int k = j0; k < j1; ++k) {                     // one image per tile (SA: tile k = part k % parts of image k / parts)
         mbar_wait(smem_u32(&bars->tmem_full[buf]), acc_phase);
         tc_fence_after();
         const uint32_t cbase = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + buf * 256;
         float best = -INFINITY;
         int bidx = 0;
-        if (p.pack_g) {                                   // geometry of tile t = k % pack_g (units start at t = 0)
+        int img = k, qoff = 0, ncols_t = p.P;
+        bool last_part = true;
+        if constexpr (SA) {
+          img = k / p.parts;
+          const int part = k - img * p.parts;
+          qoff = part * p.part_cols;
+          ncols_t = min(p.part_cols, p.P - qoff);
+          last_part = part == p.parts - 1;
+          nchunks = (ncols_t + 15) >> 4;
+          c_split = (nchunks + 1) >> 1;
+          c_lo = upper ? c_split : 0;
+          c_hi = upper ? nchunks : c_split;
+          if (!upper && part > 0) { best = run_best; bidx = run_idx; }     // earlier parts hold the lower indices
+        } else if (p.pack_g) {                            // geometry of tile t = k % pack_g (units start at t = 0)
           const int t = k % p.pack_g;
           col_off = static_cast<int>(p.pack_start[t]) - t * p.P;
           head_n = static_cast<int>(p.pack_start[t]) + static_cast<int>(p.pack_n[t]) - (t + 1) * p.P;
@@ -598,11 +636,11 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           for (int c = c_lo; c < c_end; c += 2) {
             tmem_wait_ld16(va);
             if (c + 1 < c_hi) tmem_ld16(cbase + (c + 1) * 16, vb);
-            scan16(va, c * 16 + col_off, p.P, 0, best, bidx);
+            scan16(va, c * 16 + col_off, ncols_t, qoff, best, bidx);
             if (c + 1 < c_hi) {
               tmem_wait_ld16(vb);
               if (c + 2 < c_hi) tmem_ld16(cbase + (c + 2) * 16, va);
-              scan16(vb, (c + 1) * 16 + col_off, p.P, 0, best, bidx);
+              scan16(vb, (c + 1) * 16 + col_off, ncols_t, qoff, best, bidx);
             }
           }
           if (upper && head_n > 0) {                      // the tile's last chunk again: head of the next image
@@ -632,8 +670,15 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
           __syncwarp();
           if (lane == 0) mbar_arrive_even_cta(smem_u32(&bars->tmem_empty[buf]));   // also orders xchg reuse after this read
           if (o.x > best) { best = o.x; bidx = __float_as_int(o.y); }
+          if (SA && !last_part) {                         // more parts of this image to come: carry, emit nothing yet
+            run_best = best;
+            run_idx = bidx;
+            buf ^= 1;
+            if (buf == 0) acc_phase ^= 1;
+            continue;
+          }
           if (valid && p.argmax != nullptr) {
-            const size_t off = static_cast<size_t>(k) * p.ld_arg + R;
+            const size_t off = static_cast<size_t>(img) * p.ld_arg + R;
             if (p.argmax_u16) reinterpret_cast<uint16_t*>(p.argmax)[off] = static_cast<uint16_t>(bidx);
             else if (p.l2_hint & 2) __stcs(reinterpret_cast<unsigned char*>(p.argmax) + off, static_cast<unsigned char>(bidx));
             else reinterpret_cast<uint8_t*>(p.argmax)[off] = static_cast<uint8_t>(bidx);
@@ -648,9 +693,9 @@ maxsim_fwd_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_cons
             if (same & (1u << o2)) { v += tv; nz += tn; }
           }
           if (head) {
-            if (s_slot != nullptr) s_slot[k] = v;          // fixed-order sums: this block's own slot, one writer
-            else atomicAdd(s_row + k, v);
-            if (c_row != nullptr) atomicAdd(c_row + k, nz);
+            if (s_slot != nullptr) s_slot[img] = v;        // fixed-order sums: this block's own slot, one writer
+            else atomicAdd(s_row + img, v);
+            if (c_row != nullptr) atomicAdd(c_row + img, nz);
           }
         }
         buf ^= 1;
@@ -889,9 +934,72 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
       if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs2 * sizeof(float), stream));
       if (overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem > max_smem) q.num_stages -= 1;
       const int smem2 = overhead + q.num_kb * kABlockBytes + q.num_stages * q.stage_bytes + extra_smem;
-      CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+      CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
       int ncl = q.num_units < clusters ? q.num_units : clusters;
-      maxsim_fwd_tc2_kernel<<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
+      maxsim_fwd_tc2_kernel<false><<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
+      CXL_CUDA_CHECK(cudaGetLastError());
+      if (S_extra != nullptr) return launch_maxsim_finalize_slots(S, S_extra, cnt, Bt, Bi, T, 32, mean_mode, stream);
+      return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
+    }
+  }
+  // ---- CTA-pair kernel with the text block streamed through the ring (SA): large D (text tile not resident) and / or
+  //      images of several N tiles (P > 256) -- the cfg-5 geometry (P 576 = 3 x 192 columns, D 768) ----
+  static const int pair_sa_env = getenv("CXL_K1_PAIR_STREAM") ? atoi(getenv("CXL_K1_PAIR_STREAM")) : 1;
+  if (pair_env && pair_sa_env && p.ipt == 1 && dbg == nullptr && !force_stream_a && force_grid <= 0 &&
+      p.n_tile % 16 == 0 && P > 128) {
+    const int half_bytes = (p.n_tile / 2) * kBlockK * 2;
+    const int stage_sa = kABlockBytes + round_up(half_bytes, 1024);
+    const int st = (max_smem - overhead) / stage_sa;
+    if (st >= 4) {
+      FwdTcParams q = p;
+      q.a_resident = 0;
+      q.b_block_bytes = half_bytes;
+      q.stage_bytes = stage_sa;
+      q.num_stages = st > kMaxStages ? kMaxStages : st;
+      q.num_m_tiles = (p.rows_a + 2 * kBlockM - 1) / (2 * kBlockM);      // 256-row pairs
+      const int clusters = num_sms() / 2;
+      const int n_img = (Bi + p.ipt - 1) / p.ipt;
+      // units = (256-row pair, chunk of whole images), chunk-major: all clusters stream the same images at a time.
+      // As few chunks as keep the static round-robin over clusters balanced ...
+      int chunks = 1;
+      for (; chunks < 64 && chunks < n_img; ++chunks) {
+        const long long u = static_cast<long long>(chunks) * q.num_m_tiles;
+        const long long waves = (u + clusters - 1) / clusters;
+        if (static_cast<double>(u) >= 0.97 * static_cast<double>(waves * clusters)) break;
+      }
+      int img_per_unit = (n_img + chunks - 1) / chunks;
+      // ... but no more images than stay in L2 while every wave of row pairs re-reads them (40 MB; see the block
+      // comment of the resident kernel above), when there are several waves at all
+      {
+        const long long img_bytes = static_cast<long long>(p.p_stride) * D * 2;
+        int blk = static_cast<int>((40LL << 20) / img_bytes);
+        static const int blk_env = getenv("CXL_K1_IMG_BLOCK") ? atoi(getenv("CXL_K1_IMG_BLOCK")) : -1;
+        if (blk_env >= 0) blk = blk_env;
+        if (blk > 0 && img_per_unit > blk && q.num_m_tiles >= 4 * clusters) {
+          const int nblk = (n_img + blk - 1) / blk;
+          img_per_unit = (n_img + nblk - 1) / nblk;
+        }
+      }
+      q.tiles_per_unit = img_per_unit * p.parts;
+      chunks = (q.total_n_tiles + q.tiles_per_unit - 1) / q.tiles_per_unit;
+      q.num_units = chunks * q.num_m_tiles;
+      q.mean_mode = mean_mode;
+      q.argmax_u16 = P > 256;
+      q.S = S; q.cnt = cnt; q.argmax = argmax; q.ld_arg = ld_arg; q.dbg = nullptr;
+      q.pack_g = 0;
+      q.l2_hint = 0;
+      CUtensorMap tmA2, tmB2;
+      int rc2 = make_tmap(&tmA2, txt, q.rows_a, D, kBlockM, p.f16);
+      if (rc2 != CXL_OK) return rc2;
+      rc2 = make_tmap(&tmB2, img, static_cast<long long>(Bi) * q.p_stride, D, q.n_tile / 2, p.f16);
+      if (rc2 != CXL_OK) return rc2;
+      const size_t npairs2 = static_cast<size_t>(Bt) * Bi;
+      if (S_extra == nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(S, 0, npairs2 * sizeof(float), stream));
+      if (cnt != nullptr) CXL_CUDA_CHECK(cudaMemsetAsync(cnt, 0, npairs2 * sizeof(float), stream));
+      const int smem2 = overhead + q.num_stages * q.stage_bytes;
+      CXL_CUDA_CHECK(cudaFuncSetAttribute(maxsim_fwd_tc2_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem2));
+      const int ncl = q.num_units < clusters ? q.num_units : clusters;
+      maxsim_fwd_tc2_kernel<true><<<2 * ncl, kThreads2, smem2, CXL_COUNTED(stream)>>>(tmA2, tmB2, q);
       CXL_CUDA_CHECK(cudaGetLastError());
       if (S_extra != nullptr) return launch_maxsim_finalize_slots(S, S_extra, cnt, Bt, Bi, T, 32, mean_mode, stream);
       return launch_maxsim_finalize(S, cnt, npairs2, T, mean_mode, stream);
