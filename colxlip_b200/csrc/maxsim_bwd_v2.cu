@@ -37,6 +37,7 @@ struct BwdV2Params {
   int stages;
   int stage_bytes;      // bytes of one ring stage
   int tile_bytes;       // bytes TMA delivers into a stage
+  int slab_box_rows;    // dTxt: slab rows per TMA box (P when P <= 256, else P split evenly into <= 256-row boxes)
   // dImg (one chunk of images at a time)
   const uint8_t* lists; // [chunk_n][n_st][block_bytes] row lists of the chunk (maxsim_bwd_dimg_lists_kernel)
   int n_st;             // 512-row super-tiles
@@ -108,7 +109,8 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
         const uint32_t st = smem0 + stage * stage_bytes;
         const uint32_t full = full0 + 8 * stage;
         mbar_arrive_expect_tx(full, p.tile_bytes + qbytes);
-        for (int q0 = 0; q0 < p.P; q0 += 256) tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, (p.img_k0 + k) * p.p_stride + q0);
+        for (int q0 = 0; q0 < p.P; q0 += p.slab_box_rows)
+          tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, (p.img_k0 + k) * p.p_stride + q0);
         bulk_load_1d(st + p.tile_bytes, qsrc, qbytes, full);
         if (k + 12 < Bi) bulk_prefetch_l2(qsrc + 12 * qstep, qbytes);     // argmax bytes come from DRAM: stay 12 images ahead
         qsrc += qstep;
@@ -570,10 +572,14 @@ template <int NWC, bool U16, bool F16>
 static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStream_t stream) {
   constexpr int DS = 64;
   constexpr int ROWS = NWC * 32;
-  // the TMA box covers min(P,256) slab rows; P > 256 takes several boxes (the last one may read into the next
-  // image or past the end -> zero fill; those rows are never gathered)
-  const int box_rows = p.P < 256 ? p.P : 256;
-  const int slab_rows = round_up_i(p.P, box_rows);
+  // the TMA box covers P slab rows when P <= 256; a larger P is split EVENLY into ceil(P/256) boxes (576 = 3 x 192:
+  // the stage holds exactly the image's 72 KB and three stages fit; with 256-row boxes it held 768 rows = 96 KB, a
+  // third of them the next image's, and only two stages fit).  A box that is rounded up may read into the next image
+  // or past the end (zero fill); those rows are never gathered.
+  const int n_box = (p.P + 255) / 256;
+  const int box_rows = p.P <= 256 ? p.P : round_up_i((p.P + n_box - 1) / n_box, 8);
+  const int slab_rows = n_box * box_rows;
+  p.slab_box_rows = box_rows;
   p.tile_bytes = slab_rows * DS * 2;
   p.stage_bytes = round_up_i(p.tile_bytes + ROWS * (U16 ? 2 : 1), 128);
   const int overhead = 128 + static_cast<int>(sizeof(V2Barriers)) + NWC * 256;
