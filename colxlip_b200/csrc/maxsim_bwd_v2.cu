@@ -38,6 +38,7 @@ struct BwdV2Params {
   int stage_bytes;      // bytes of one ring stage
   int tile_bytes;       // bytes TMA delivers into a stage
   int slab_box_rows;    // dTxt: slab rows per TMA box (P when P <= 256, else P split evenly into <= 256-row boxes)
+  int slab_n_box;       // dTxt: TMA boxes per slab (even when row-tile pairs share them by multicast)
   // dImg (one chunk of images at a time)
   const uint8_t* lists; // [chunk_n][n_st][block_bytes] row lists of the chunk (maxsim_bwd_dimg_lists_kernel)
   int n_st;             // 512-row super-tiles
@@ -62,7 +63,13 @@ struct __align__(8) V2Barriers {
 // image AND the CTA's slice of that image's argmax row (ROWS contiguous elements, one bulk copy), so no
 // consumer ever waits on a global load for its indices.  Lane = 8*qw + l8: quarter qw handles rows 4*jj + qw
 // (jj = 0..7) of its warp, l8 selects the 8-channel chunk of the 64-wide slice.
-template <int NWC, bool U16, bool F16>
+// MC = true: clusters of two row-tile CTAs of the same D slice.  Both walk the same images in the same order, so each
+// CTA loads HALF of every slab's TMA boxes and multicasts them into both CTAs' stages (L2 -> SM traffic of the slabs
+// halves; at P = 576 the kernel is bound by exactly that).  A stage may be overwritten only when the consumers of BOTH
+// CTAs have released it: every consumer warp arrives on both CTAs' empty barriers (count 2 * NWC).  The argmax slice
+// of a stage stays private.  A CTA past the last row tile (odd number of tiles) takes part in the protocol and stores
+// nothing.
+template <int NWC, bool U16, bool F16, bool MC>
 __global__ void __launch_bounds__((NWC + 1) * 32, 1)
 maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2Params p) {
   constexpr int DS = 64;
@@ -84,20 +91,23 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
   const uint32_t full0 = smem_u32(&bars->full[0]);
   const uint32_t empty0 = smem_u32(&bars->empty[0]);
 
+  const uint32_t crank = MC ? cluster_ctarank() : 0u;
   if (threadIdx.x == 0) {
     for (int s = 0; s < stages; ++s) {
       mbar_init(full0 + 8 * s, 1);
-      mbar_init(empty0 + 8 * s, NWC);
+      mbar_init(empty0 + 8 * s, MC ? 2 * NWC : NWC);
     }
     fence_barrier_init();
     tma_prefetch_desc(&tmImg);
   }
   __syncthreads();
+  if constexpr (MC) cluster_sync_all();                   // the peer's barriers exist before anything is sent to them
 
   if (warp == NWC) {
     if (lane == 0) {
       // argmax elements of this CTA's rows (clamped to the padded row length; both multiples of 16 bytes)
-      const long long avail = p.arg_avail - r0;
+      long long avail = p.arg_avail - r0;
+      if (avail < 0) avail = 0;                            // MC: the CTA past the last row tile has no rows
       const uint32_t qbytes = static_cast<uint32_t>((avail < ROWS ? avail : ROWS) * ES);
       const uint8_t* qsrc = reinterpret_cast<const uint8_t*>(p.argmax) +
                             (static_cast<size_t>(p.k_off) * p.ld_arg + r0) * ES;
@@ -109,14 +119,26 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
         const uint32_t st = smem0 + stage * stage_bytes;
         const uint32_t full = full0 + 8 * stage;
         mbar_arrive_expect_tx(full, p.tile_bytes + qbytes);
-        for (int q0 = 0; q0 < p.P; q0 += p.slab_box_rows)
-          tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, (p.img_k0 + k) * p.p_stride + q0);
-        bulk_load_1d(st + p.tile_bytes, qsrc, qbytes, full);
-        if (k + 12 < Bi) bulk_prefetch_l2(qsrc + 12 * qstep, qbytes);     // argmax bytes come from DRAM: stay 12 images ahead
+        if constexpr (MC) {                                // boxes crank, crank + 2, ...: into both CTAs of the pair
+          for (int b = static_cast<int>(crank); b < p.slab_n_box; b += 2) {
+            const int q0 = b * p.slab_box_rows;
+            tma_load_2d_mc(st + q0 * DS * 2, &tmImg, full, d0, (p.img_k0 + k) * p.p_stride + q0, 3);
+          }
+        } else {
+          for (int b = 0; b < p.slab_n_box; ++b) {
+            const int q0 = b * p.slab_box_rows;
+            tma_load_2d(st + q0 * DS * 2, &tmImg, full, d0, (p.img_k0 + k) * p.p_stride + q0);
+          }
+        }
+        if (qbytes > 0) {
+          bulk_load_1d(st + p.tile_bytes, qsrc, qbytes, full);
+          if (k + 12 < Bi) bulk_prefetch_l2(qsrc + 12 * qstep, qbytes);   // argmax bytes come from DRAM: stay 12 images ahead
+        }
         qsrc += qstep;
         if (++stage == stages) { stage = 0; phase ^= 1; }
       }
     }
+    if constexpr (MC) cluster_sync_all();                 // pairs with the consumers' exit barrier below
     return;
   }
 
@@ -198,7 +220,11 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
           fhfma8_lo<F16>(acc[jj], v, e[jj]);
         }
         __syncwarp();
-        if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+        if constexpr (MC) {
+          if (lane < 2) mbar_arrive_cluster(empty0 + 8 * stage, lane);     // this warp is done with the slot in BOTH CTAs' eyes
+        } else {
+          if (lane == 0) mbar_arrive(empty0 + 8 * stage);
+        }
         stage = nstage;
         phase = nphase;
       }
@@ -213,6 +239,7 @@ maxsim_bwd_dtxt_v2_kernel(const __grid_constant__ CUtensorMap tmImg, const BwdV2
       *reinterpret_cast<float4*>(o + 4) = make_float4(acc[jj][4] * w_inv, acc[jj][5] * w_inv, acc[jj][6] * w_inv, acc[jj][7] * w_inv);
     }
   }
+  if constexpr (MC) cluster_sync_all();                   // the peer may still arrive on this CTA's barriers
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -568,18 +595,19 @@ int env_int(const char* name, int dflt) {
   return (s != nullptr && *s != 0) ? atoi(s) : dflt;
 }
 
-template <int NWC, bool U16, bool F16>
-static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStream_t stream) {
+template <int NWC, bool U16, bool F16, bool MC>
+static int launch_dtxt_v2_k(const void* img, BwdV2Params p, int max_smem, cudaStream_t stream) {
   constexpr int DS = 64;
   constexpr int ROWS = NWC * 32;
   // the TMA box covers P slab rows when P <= 256; a larger P is split EVENLY into ceil(P/256) boxes (576 = 3 x 192:
   // the stage holds exactly the image's 72 KB and three stages fit; with 256-row boxes it held 768 rows = 96 KB, a
   // third of them the next image's, and only two stages fit).  A box that is rounded up may read into the next image
-  // or past the end (zero fill); those rows are never gathered.
-  const int n_box = (p.P + 255) / 256;
-  const int box_rows = p.P <= 256 ? p.P : round_up_i((p.P + n_box - 1) / n_box, 8);
+  // or past the end (zero fill); those rows are never gathered.  MC: an even number of boxes, half per CTA of the pair.
+  const int n_box = MC ? 2 * ((p.P + 511) / 512) : (p.P + 255) / 256;
+  const int box_rows = (!MC && p.P <= 256) ? p.P : round_up_i((p.P + n_box - 1) / n_box, 8);
   const int slab_rows = n_box * box_rows;
   p.slab_box_rows = box_rows;
+  p.slab_n_box = n_box;
   p.tile_bytes = slab_rows * DS * 2;
   p.stage_bytes = round_up_i(p.tile_bytes + ROWS * (U16 ? 2 : 1), 128);
   const int overhead = 128 + static_cast<int>(sizeof(V2Barriers)) + NWC * 256;
@@ -590,9 +618,11 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
   CUtensorMap tm;
   int rc = make_tmap_plain(&tm, img, static_cast<long long>(p.Bi) * p.p_stride, p.D, DS, box_rows, F16);
   if (rc != CXL_OK) return rc;
-  auto kern = maxsim_bwd_dtxt_v2_kernel<NWC, U16, F16>;
+  auto kern = maxsim_bwd_dtxt_v2_kernel<NWC, U16, F16, MC>;
   CXL_CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-  dim3 grid((p.rows + ROWS - 1) / ROWS, p.D / DS);
+  int gx = (p.rows + ROWS - 1) / ROWS;
+  if (MC) gx = (gx + 1) & ~1;                             // whole pairs; the extra CTA only takes part in the protocol
+  dim3 grid(gx, p.D / DS);
   // Image blocks: every CTA of a D slice streams the same [P,64] slabs, but the CTAs of later waves start
   // while earlier ones are mid-stream, so without blocking each CTA ends up pulling its slabs from DRAM
   // (measured at cfg-2: 25.8 TB of DRAM reads, 88 % of HBM bandwidth, L2 hit 31 %).  One launch per block of
@@ -608,10 +638,39 @@ static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStre
     p.k_off = k_off + k0;
     p.img_k0 = k0;
     p.accumulate_txt = (k0 > 0) || acc_first;
-    kern<<<grid, (NWC + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, p);
+    if (MC) {
+      cudaLaunchConfig_t cfg = {};
+      cfg.gridDim = grid;
+      cfg.blockDim = dim3((NWC + 1) * 32);
+      cfg.dynamicSmemBytes = smem_bytes;
+      cfg.stream = stream;
+      cudaLaunchAttribute attr[1];
+      attr[0].id = cudaLaunchAttributeClusterDimension;
+      attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+      cfg.attrs = attr;
+      cfg.numAttrs = 1;
+      note_launch();
+      CXL_CUDA_CHECK(cudaLaunchKernelEx(&cfg, kern, tm, p));
+    } else {
+      kern<<<grid, (NWC + 1) * 32, smem_bytes, CXL_COUNTED(stream)>>>(tm, p);
+    }
     CXL_CUDA_CHECK(cudaGetLastError());
   }
   return CXL_OK;
+}
+
+// CXL_DTXT_MC: 0 (default) = independent CTAs, 1 = row-tile pairs with multicast slabs for P > 256, 2 = always.
+// NEGATIVE RESULT (one B200, interleaved, profiles/r4x_dtxt_multicast_ab.txt): bit-identical output, but 61.9 vs 39.2 ms
+// at P 576 / D 768 (B 2048) and 133.1 vs 55.5 ms at P 196 / D 512 (B 4096).  Halving the L2 -> SM slab traffic does not
+// pay for coupling the two CTAs: a stage is refilled only when BOTH CTAs' 15 consumer warps have released it (remote
+// mbarrier arrives), so the pair runs at the pace of its slower half with the latency of a cluster round trip per
+// stage, and the 3-6 stage ring is too shallow to absorb that.  Kept as an option for A/B.
+template <int NWC, bool U16, bool F16>
+static int launch_dtxt_v2(const void* img, BwdV2Params p, int max_smem, cudaStream_t stream) {
+  const int mc = env_int("CXL_DTXT_MC", 0);
+  const bool use_mc = (mc >= 2 || (mc == 1 && p.P > 256)) && p.rows > NWC * 32;
+  if (use_mc) return launch_dtxt_v2_k<NWC, U16, F16, true>(img, p, max_smem, stream);
+  return launch_dtxt_v2_k<NWC, U16, F16, false>(img, p, max_smem, stream);
 }
 
 // One chunk of images: lists pre-pass, then the gather kernel.  `p.lists` is scratch for chunk_cap images.

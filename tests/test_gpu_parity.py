@@ -398,3 +398,27 @@ def test_properties_at_scale(K):
     assert (got - checksum).abs().max() <= 2e-2 * checksum.abs().max()   # grads were rounded to bf16 on return
     checksum_t = torch.einsum("mnd->m", gt1)
     assert torch.isfinite(checksum_t).all()
+
+
+@pytest.mark.parametrize("shape", [(300, 11, 77, 196, 512), (33, 12, 77, 576, 768), (130, 5, 20, 300, 128), (40, 9, 33, 576, 128)],
+                         ids=str)
+def test_dtxt_row_tile_pairs_with_multicast_slabs_are_bit_identical(K, shape, monkeypatch):
+    """dTxt in clusters of two row-tile CTAs that share every image slab by TMA multicast (opt-in, CXL_DTXT_MC=2;
+    measured slower than independent CTAs, kept for A/B): the same additions in the same order, so the same bits --
+    including an odd number of row tiles (the extra CTA of the last pair only takes part in the barrier protocol)."""
+    Bt, Bi, T, P, D = shape
+    _, _, ti, tt = O.synth_inputs(Bi, P, T, D, seed=5 + P, pad_text=True, Bt=Bt)
+    ti, tt = ti.to(torch.bfloat16).cuda(), tt.to(torch.bfloat16).cuda()
+    txt_op = K.prepare(tt, T, "bf16")
+    img_op = K.prepare(ti, K.img_row_stride(P, "bf16"), "bf16")
+    S, cnt, arg = K.maxsim_fwd(txt_op, img_op, T, P, "bf16", O.MASKED, True)
+    w = K.pair_weights(torch.randn(Bt, Bi, device="cuda") * 1e-3, cnt, T, O.MASKED)
+    outs = []
+    for mc in ("0", "2"):
+        monkeypatch.setenv("CXL_DTXT_MC", mc)
+        dtxt, _ = K.maxsim_bwd(txt_op, img_op, arg, w, T, P, "bf16", need_img=False)
+        part = K.maxsim_bwd_dtxt_rows(img_op, arg, w, Bt, 16, min(8, Bt - 16), T, P, "bf16")
+        torch.cuda.synchronize()
+        outs.append((dtxt.clone(), part.clone()))
+    assert torch.equal(outs[0][0], outs[1][0]) and torch.equal(outs[0][1], outs[1][1])
+    assert torch.isfinite(outs[1][0]).all() and outs[1][0].abs().sum().item() > 0
