@@ -968,11 +968,14 @@ int maxsim_fwd_tc(const void* txt, const void* img, int Bt, int Bi, int T, int P
         if (static_cast<double>(u) >= 0.97 * static_cast<double>(waves * clusters)) break;
       }
       int img_per_unit = (n_img + chunks - 1) / chunks;
-      // ... but no more images than stay in L2 while every wave of row pairs re-reads them (40 MB; see the block
-      // comment of the resident kernel above), when there are several waves at all
+      // ... but no more images than stay in L2 while every wave of row pairs re-reads them, when there are several waves
+      // at all.  The streamed text tiles of a wave (74 x 393 KB = 29 MB at D = 768) live in L2 next to the block and
+      // each die keeps its own copy, so the block is small: 14 MB = 16 images at cfg-5.  One B200, [8192 x 8192] launch,
+      // P 576 / D 768: no blocks 1020 TF/s, 4 images 1298, 8 1311, 16 1308-1313, 24 1306, 47 1286-1291, 96 1246
+      // (profiles/r4z_k1_sa_block.txt)
       {
         const long long img_bytes = static_cast<long long>(p.p_stride) * D * 2;
-        int blk = static_cast<int>((40LL << 20) / img_bytes);
+        int blk = static_cast<int>((14LL << 20) / img_bytes);
         static const int blk_env = getenv("CXL_K1_IMG_BLOCK") ? atoi(getenv("CXL_K1_IMG_BLOCK")) : -1;
         if (blk_env >= 0) blk = blk_env;
         if (blk > 0 && img_per_unit > blk && q.num_m_tiles >= 4 * clusters) {
