@@ -29,6 +29,16 @@ int main(void) {
   fails += cxl_maxsim_fwd(NULL, NULL, 1, 1, 1, 1, 64, CXL_DTYPE_BF16, CXL_MEAN_MASKED, NULL, NULL, NULL, NULL) !=
            CXL_ERR_INVALID_ARG;
   fails += cxl_l2norm_fwd(NULL, CXL_DTYPE_F32, 1, 8, NULL, CXL_DTYPE_BF16, NULL, NULL) != CXL_ERR_INVALID_ARG;
+  /* workspace queries are pure arithmetic: the fixed-order score sums of cxl_maxsim_fwd_ws keep (T+30)/32 extra
+   * [Bt,Bi] f32 slots (T = 77 -> 3), cxl_infonce_grad_ws one float per block, the statistics pass 2 floats per
+   * (128-row block, column); the allocation-free statistics entry refuses what exceeds its built-in 16 MiB */
+  fails += cxl_maxsim_fwd_workspace_bytes(64, 32, 77, CXL_DTYPE_BF16) != (size_t)3 * 64 * 32 * 4;
+  fails += cxl_infonce_grad_workspace_bytes(100, 4096) != (size_t)2 * 100 * 4;
+  fails += cxl_infonce_workspace_bytes(256, 1000) != (size_t)2 * 2 * 1000 * 4;
+  fails += cxl_infonce_workspace_bytes(16384, 32768) <= CXL_INFONCE_STATIC_SCRATCH_BYTES;
+  fails += strstr(cxl_strerror(CXL_ERR_STATIC_SCRATCH), "static scratch") == NULL;
+  fails += cxl_maxsim_fwd_ws(NULL, NULL, 1, 1, 1, 1, 64, CXL_DTYPE_BF16, CXL_MEAN_MASKED | CXL_MEAN_ROUND16, NULL, NULL, NULL,
+                             NULL, 0, NULL) != CXL_ERR_WORKSPACE;
   printf("kernel launches so far %llu\n", cxl_kernel_launches());
   printf(fails ? "CABI_PROBE FAILED (%d)\n" : "CABI_PROBE OK\n", fails);
   return fails != 0;
