@@ -36,9 +36,12 @@ def _argmax_mismatches_are_ties(ours, ref_arg, ti, tt, what):
     return n_bad
 
 
-@pytest.mark.parametrize("shape", [(1024, 1024, 77, 196, 512), (600, 1000, 77, 196, 512)], ids=str)
+@pytest.mark.parametrize("shape", [(1024, 1024, 77, 196, 512), (600, 1000, 77, 196, 512),
+                                   (1024, 48, 77, 576, 768), (1024, 64, 77, 196, 768)], ids=str)
 def test_pair_kernel_whole_matrix_vs_device_oracle(K, shape):
-    """CTA-pair K1 (128 < P <= 256) at B ~ 1024: EVERY score, count and argmax against the oracle on the device."""
+    """CTA-pair K1 at Bt ~ 1024 (clusters run many units, rings wrap, image blocks engage): EVERY score, count and
+    argmax against the oracle on the device.  D = 512: resident text tile; D = 768: the streamed-A variant, with an
+    image in three 192-column parts (P = 576) and in one tile (P = 196)."""
     Bt, Bi, T, P, D = shape
     _, _, ti, tt = _device_inputs(Bi, P, T, D, seed=2024, Bt=Bt)
     txt_op = K.prepare(tt, T, "bf16")
