@@ -397,3 +397,24 @@ def test_fused_token_head(N, T, width, D, dtype):
     assert (xr.grad - xr2.grad).abs().max() <= 2e-2 * xr2.grad.abs().max() + 1e-6
     for (n1, p1), (n2, p2) in zip(head.named_parameters(), ref.named_parameters()):
         assert (p1.grad - p2.grad).abs().max() <= 2e-2 * p2.grad.abs().max() + 1e-6, n1
+
+
+def test_nvtx_ranges_bracket_the_phases_of_a_step(monkeypatch):
+    """the fused loss opens one NVTX range per phase (K1, K3 statistics, K3 gradient, K2, last reduction)
+    and closes every range it opened."""
+    from colxlip_b200 import ColClipLoss
+    events = []
+    monkeypatch.setattr(torch.cuda.nvtx, "range_push", lambda name: events.append(("push", name)))
+    monkeypatch.setattr(torch.cuda.nvtx, "range_pop", lambda: events.append(("pop", None)))
+    xs = [t.cuda().requires_grad_() for t in O.synth_inputs(16, 196, 20, 128, seed=3)]
+    ls = torch.tensor(10.0, device="cuda", requires_grad=True)
+    ColClipLoss()(*xs, ls, output_dict=True)["total_loss"].backward()
+    torch.cuda.synchronize()
+    names = [n for kind, n in events if kind == "push"]
+    assert len(names) == 5 and all(n.startswith("cxl: ") for n in names)
+    assert "K1" in names[0] and "K3 statistics" in names[1] and "K2" in names[3]
+    depth = 0
+    for kind, _ in events:
+        depth += 1 if kind == "push" else -1
+        assert 0 <= depth <= 1
+    assert depth == 0
